@@ -1,0 +1,254 @@
+"""Host-side binding of libdcb200.so (include/dc_b200.h) for Python callers.
+
+PyTorch is plumbing only (device memory, streams, torch.distributed); every byte of codec work happens in
+the hand-written sm_100a kernels behind the C ABI.  There is NO CPU path: loading fails loudly when the
+library is missing, and every call raises when there is no CUDA device.
+
+Naming follows the reference (impl/dataCompression.h): compress types CT=5/6/7/11 (+8/9 with CRC),
+absErrorBound, streams / chunks / min / medium / type / mask.
+"""
+import ctypes as C
+import os
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "libdcb200.so")
+
+CT_BITWISE, CT_BITWISE_NP, CT_BITWISE_MASK, CT_BITWISE_CRC, CT_MASK_CRC, CT_BITWISE_OP = 5, 6, 7, 8, 9, 11
+F_SUBTRACT_MIN, F_FIXED_MASK, F_CRC = 1, 2, 4
+TILE_ELEMS = 4096
+DEFAULT_CHUNK = 4096
+
+ERRORS = {-1: "DCB_EINVAL (bad argument)", -2: "DCB_ECAPACITY (buffer too small)", -3: "DCB_ECUDA",
+          -4: "DCB_ENODEVICE (no CUDA device; there is no CPU fallback)", -5: "DCB_EFORMAT (malformed stream)"}
+
+EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb", "dcb_num_chunks",
+           "dcb_max_stream_bytes", "dcb_workspace_bytes", "dcb_compress", "dcb_decompress", "dcb_crc32_chunks",
+           "dcb_chunk_stats", "dcb_flip_bits", "dcb_compress_host", "dcb_decompress_host"]
+
+_lib = None
+
+
+class DcbError(RuntimeError):
+    pass
+
+
+def lib():
+    """Loads libdcb200.so (no implicit build, no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise DcbError("libdcb200.so is not built: run `python -m data_compression_b200.build` "
+                           "(or __graft_entry__.build()); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        vp, u64, u32, i32, dbl = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_double
+        L.dcb_version.restype = C.c_char_p
+        L.dcb_last_cuda_error.restype = C.c_char_p
+        L.dcb_device_count.restype = i32
+        L.dcb_n_eb.restype = i32
+        L.dcb_n_eb.argtypes = [dbl]
+        for f in ("dcb_num_chunks", "dcb_max_stream_bytes", "dcb_workspace_bytes"):
+            getattr(L, f).restype = u64
+            getattr(L, f).argtypes = [u64, u64]
+        L.dcb_compress.restype = i32
+        L.dcb_compress.argtypes = [i32, vp, u64, u64, dbl, u32, i32, u32, vp, u64, vp, vp, vp, vp, vp, vp, u64, vp]
+        L.dcb_decompress.restype = i32
+        L.dcb_decompress.argtypes = [i32, vp, vp, u64, u64, dbl, u32, i32, u32, vp, vp, vp, vp, vp, vp]
+        L.dcb_crc32_chunks.restype = i32
+        L.dcb_crc32_chunks.argtypes = [vp, vp, u64, vp, vp]
+        L.dcb_chunk_stats.restype = i32
+        L.dcb_chunk_stats.argtypes = [vp, u64, u64, i32, vp, vp, vp, vp]
+        L.dcb_flip_bits.restype = i32
+        L.dcb_flip_bits.argtypes = [vp, vp, u64, vp]
+        L.dcb_compress_host.restype = i32
+        L.dcb_compress_host.argtypes = [i32, vp, u64, u64, dbl, u32, i32, u32, vp, vp, vp, vp, vp, vp]
+        L.dcb_decompress_host.restype = i32
+        L.dcb_decompress_host.argtypes = [i32, vp, vp, u64, u64, dbl, u32, i32, u32, vp, vp, vp, vp]
+        _lib = L
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        extra = ""
+        if rc == -3:
+            extra = ": " + lib().dcb_last_cuda_error().decode()
+        raise DcbError("%s failed: %s%s" % (what, ERRORS.get(rc, rc), extra))
+
+
+def n_eb(abs_error_bound):
+    return lib().dcb_n_eb(abs_error_bound)
+
+
+def num_chunks(n, chunk_elems):
+    return lib().dcb_num_chunks(n, chunk_elems)
+
+
+def mask17_of(medium):
+    """First 17 bits (sign, exponent, 8 mantissa bits) of `medium`: the char mask[17] of impl/pingpong.c:202-206."""
+    return int(np.array([medium], dtype=np.float32).view(np.uint32)[0] >> 15)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _cur_stream(device):
+    import torch
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+@dataclass
+class Compressed:
+    """Device-resident result of compress(): the reference's byte stream(s) plus the chunk table."""
+    ct: int
+    n: int
+    chunk_elems: int
+    abs_error_bound: float
+    flags: int
+    fixed_type: int
+    fixed_mask17: int
+    stream: "object"                  # uint8 [capacity]; valid bytes = total_bytes()
+    chunk_offsets: "object"           # uint64-as-int64 [K+1]
+    chunk_min: Optional["object"]     # float32 [K]
+    chunk_medium: Optional["object"]  # float32 [K] (CT=7/9 per-chunk mask)
+    chunk_type: Optional["object"]    # int32 [K]
+    chunk_crc: Optional["object"]     # uint32-as-int32 [K] (CT=8/9)
+
+    @property
+    def num_chunks(self):
+        return self.chunk_offsets.numel() - 1
+
+    def total_bytes(self):
+        return int(self.chunk_offsets[-1].item())
+
+    def ratio(self):
+        return 4.0 * self.n / max(self.total_bytes(), 1)
+
+    def stream_bytes(self):
+        return self.stream[: self.total_bytes()]
+
+
+class Workspace:
+    """Reusable device buffers for one (n, chunk_elems) shape, so that a timed loop does no allocation."""
+
+    def __init__(self, n, chunk_elems, device):
+        import torch
+        L = lib()
+        self.n, self.chunk_elems, self.device = n, chunk_elems, device
+        K = L.dcb_num_chunks(n, chunk_elems)
+        self.K = K
+        self.capacity = L.dcb_max_stream_bytes(n, chunk_elems)
+        self.stream = torch.empty(self.capacity, dtype=torch.uint8, device=device)
+        self.offsets = torch.zeros(K + 1, dtype=torch.int64, device=device)
+        self.cmin = torch.zeros(max(K, 1), dtype=torch.float32, device=device)
+        self.cmed = torch.zeros(max(K, 1), dtype=torch.float32, device=device)
+        self.ctype = torch.zeros(max(K, 1), dtype=torch.int32, device=device)
+        self.ccrc = torch.zeros(max(K, 1), dtype=torch.int32, device=device)
+        self.ws_bytes = L.dcb_workspace_bytes(n, chunk_elems)
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=device)
+        self.status = torch.zeros(1, dtype=torch.int32, device=device)
+
+
+def compress(x, ct=CT_BITWISE, abs_error_bound=1e-6, chunk_elems=DEFAULT_CHUNK, subtract_min=True,
+             fixed_type=None, fixed_mask17=None, crc=False, workspace=None):
+    """x: contiguous float32 CUDA tensor.  One chunk == one reference call myCompress_bitwise*(..., (NULL,0,8))."""
+    import torch
+    if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()):
+        raise DcbError("compress() needs a contiguous float32 CUDA tensor (there is no CPU path)")
+    n = x.numel()
+    ws = workspace or Workspace(n, chunk_elems, x.device)
+    flags = (F_SUBTRACT_MIN if subtract_min else 0) | (F_CRC if crc else 0)
+    ft, fm = 0, 0
+    if fixed_type is not None:
+        flags |= F_FIXED_MASK
+        ft, fm = int(fixed_type), int(fixed_mask17)
+    with torch.cuda.device(x.device):
+        rc = lib().dcb_compress(ct, _ptr(x), n, chunk_elems, abs_error_bound, flags, ft, fm, _ptr(ws.stream),
+                                ws.capacity, _ptr(ws.offsets), _ptr(ws.cmin), _ptr(ws.cmed), _ptr(ws.ctype),
+                                _ptr(ws.ccrc), _ptr(ws.ws), ws.ws_bytes, _cur_stream(x.device))
+    check(rc, "dcb_compress")
+    has_crc = crc or ct in (CT_BITWISE_CRC, CT_MASK_CRC)
+    per_chunk_mask = ct in (CT_BITWISE_MASK, CT_MASK_CRC) and fixed_type is None
+    return Compressed(ct, n, chunk_elems, abs_error_bound, flags, ft, fm, ws.stream, ws.offsets,
+                      ws.cmin if subtract_min else None, ws.cmed if per_chunk_mask else None,
+                      ws.ctype if per_chunk_mask else None, ws.ccrc if has_crc else None)
+
+
+def decompress(comp, out=None, status=None):
+    import torch
+    dev = comp.stream.device
+    if out is None:
+        out = torch.empty(comp.n, dtype=torch.float32, device=dev)
+    if status is None:
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib().dcb_decompress(comp.ct, _ptr(comp.stream), _ptr(comp.chunk_offsets), comp.n, comp.chunk_elems,
+                                  comp.abs_error_bound, comp.flags & 3, comp.fixed_type, comp.fixed_mask17,
+                                  _ptr(comp.chunk_min), _ptr(comp.chunk_medium), _ptr(comp.chunk_type), _ptr(out),
+                                  _ptr(status), _cur_stream(dev))
+    check(rc, "dcb_decompress")
+    return out
+
+
+def crc32_chunks(stream, chunk_offsets):
+    import torch
+    K = chunk_offsets.numel() - 1
+    out = torch.zeros(max(K, 1), dtype=torch.int32, device=stream.device)
+    with torch.cuda.device(stream.device):
+        check(lib().dcb_crc32_chunks(_ptr(stream), _ptr(chunk_offsets), K, _ptr(out), _cur_stream(stream.device)),
+              "dcb_crc32_chunks")
+    return out[:K]
+
+
+def flip_bits(stream, bit_indices):
+    """bit_flip test hook (dataCompression.c:5858): flips the given stream bits in place."""
+    import torch
+    idx = torch.as_tensor(bit_indices, dtype=torch.int64, device=stream.device)
+    with torch.cuda.device(stream.device):
+        check(lib().dcb_flip_bits(_ptr(stream), _ptr(idx), idx.numel(), _cur_stream(stream.device)), "dcb_flip_bits")
+
+
+# ---- host-pointer layer (numpy in, numpy out; H2D/D2H inside the C library) -------------------------------
+def compress_host(x, ct=CT_BITWISE, abs_error_bound=1e-6, chunk_elems=DEFAULT_CHUNK, subtract_min=True,
+                  fixed_type=None, fixed_mask17=None, crc=False, out=None):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n = x.size
+    L = lib()
+    K = L.dcb_num_chunks(n, chunk_elems)
+    o = out or {}
+    stream = o.get("stream")
+    if stream is None:
+        stream = np.empty(L.dcb_max_stream_bytes(n, chunk_elems), dtype=np.uint8)
+    offs = np.zeros(K + 1, dtype=np.uint64)
+    cmin, cmed = np.zeros(max(K, 1), np.float32), np.zeros(max(K, 1), np.float32)
+    ctype, ccrc = np.zeros(max(K, 1), np.int32), np.zeros(max(K, 1), np.uint32)
+    flags = (F_SUBTRACT_MIN if subtract_min else 0) | (F_CRC if crc else 0)
+    ft, fm = 0, 0
+    if fixed_type is not None:
+        flags |= F_FIXED_MASK
+        ft, fm = int(fixed_type), int(fixed_mask17)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    check(L.dcb_compress_host(ct, vp(x), n, chunk_elems, abs_error_bound, flags, ft, fm, vp(stream), vp(offs),
+                              vp(cmin), vp(cmed), vp(ctype), vp(ccrc)), "dcb_compress_host")
+    return dict(ct=ct, n=n, chunk_elems=chunk_elems, abs_error_bound=abs_error_bound, flags=flags, fixed_type=ft,
+                fixed_mask17=fm, stream=stream, total_bytes=int(offs[K]) if n else 0, offsets=offs,
+                chunk_min=cmin[:K], chunk_medium=cmed[:K], chunk_type=ctype[:K], chunk_crc=ccrc[:K])
+
+
+def decompress_host(enc, out=None):
+    L = lib()
+    n = enc["n"]
+    if out is None:
+        out = np.empty(n, dtype=np.float32)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    per_chunk_mask = enc["ct"] in (CT_BITWISE_MASK, CT_MASK_CRC) and not (enc["flags"] & F_FIXED_MASK)
+    check(L.dcb_decompress_host(enc["ct"], vp(enc["stream"]), vp(enc["offsets"]), n, enc["chunk_elems"],
+                                enc["abs_error_bound"], enc["flags"] & 3, enc["fixed_type"], enc["fixed_mask17"],
+                                vp(enc["chunk_min"]) if (enc["flags"] & F_SUBTRACT_MIN) else None,
+                                vp(enc["chunk_medium"]) if per_chunk_mask else None,
+                                vp(enc["chunk_type"]) if per_chunk_mask else None, vp(out)), "dcb_decompress_host")
+    return out

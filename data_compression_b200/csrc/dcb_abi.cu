@@ -1,0 +1,308 @@
+// dcb_abi.cu -- extern "C" entry points of libdcb200.so (include/dc_b200.h).
+// Host logic only: argument checks, error-bound constants, launch configuration.  No CPU codec lives
+// here: without a CUDA device every entry point returns DCB_ENODEVICE.
+#include "../../include/dc_b200.h"
+#include "dcb_common.cuh"
+#include "dcb_encode.cuh"
+#include "dcb_decode.cuh"
+#include "dcb_stats.cuh"
+#include "dcb_crc.cuh"
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+static thread_local char g_err[256] = "";
+static int cuda_fail(cudaError_t e, const char* what) {
+  snprintf(g_err, sizeof g_err, "%s: %s", what, cudaGetErrorString(e));
+  return DCB_ECUDA;
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return cuda_fail(e_, #call); } while (0)
+
+extern "C" const char* dcb_version(void) { return "dcb200 0.1 (sm_100a)"; }
+extern "C" const char* dcb_last_cuda_error(void) { return g_err; }
+extern "C" int dcb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+// to_absErrorBound_binary, dataCompression.c:5512-5522 (2^-n is exact in double, no pow() needed)
+extern "C" int dcb_n_eb(double eb) {
+  for (int n = 0; n < 100; n++)
+    if (eb >= ldexp(1.0, -n)) return n;
+  return -1;
+}
+
+static int make_const(double eb, CodecConst* k) {
+  const int n_eb = dcb_n_eb(eb);
+  if (!(eb > 0.0) || n_eb < 0) return DCB_EINVAL;      // reference: undefined (falls off the end of the function)
+  k->n_eb = n_eb;
+  k->n_eb_m118 = n_eb - 118;
+  // the reference compares float32 values with the double literal absErrorBound in DOUBLE precision
+  // (:3390 fabs(x) < eb, :3399 diff_min <= eb); the same predicates on float32 thresholds:
+  float t = (float)eb;                                  // may round up
+  if (isinf(t)) t = 3.402823466e38f;
+  while ((double)t > eb) t = nextafterf(t, -INFINITY);
+  k->tp = t;                                            // largest float <= eb
+  while ((double)t >= eb) t = nextafterf(t, -INFINITY);
+  k->tz = t;                                            // largest float <  eb
+  return DCB_OK;
+}
+
+static int base_ct(int ct, uint32_t* flags) {
+  switch (ct) {
+    case DCB_CT_BITWISE: return CT_BITWISE;
+    case DCB_CT_BITWISE_NP: return CT_NP;
+    case DCB_CT_BITWISE_MASK: return CT_MASK;
+    case DCB_CT_BITWISE_OP: return CT_OP;
+    case DCB_CT_BITWISE_CRC: *flags |= DCB_F_CRC; return CT_BITWISE;   // impl/pingpong.c:260-274
+    case DCB_CT_MASK_CRC: *flags |= DCB_F_CRC; return CT_MASK;         // impl/pingpong.c:275-289
+    default: return -1;
+  }
+}
+
+static bool single_chunk(uint64_t n, uint64_t chunk) { return chunk == 0 || chunk >= n; }
+
+extern "C" uint64_t dcb_num_chunks(uint64_t n, uint64_t chunk) {
+  if (n == 0) return 0;
+  return single_chunk(n, chunk) ? 1 : (n + chunk - 1) / chunk;
+}
+extern "C" uint64_t dcb_max_stream_bytes(uint64_t n, uint64_t chunk) { (void)chunk; return 4 * n + 16; }
+static uint64_t num_tiles(uint64_t n) { return (n + DCB_TILE - 1) / DCB_TILE; }
+extern "C" uint64_t dcb_workspace_bytes(uint64_t n, uint64_t chunk) {
+  (void)chunk;
+  return 256 + 8 * num_tiles(n);
+}
+
+template <int CT>
+static cudaError_t launch_encode(const EncArgs& a, cudaStream_t st) {
+  dcb_encode_kernel<CT><<<a.num_tiles, DCB_NT, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+extern "C" int dcb_chunk_stats(const float* d_in, uint64_t n, uint64_t chunk, int want_medium,
+                               float* d_chunk_min, float* d_chunk_medium, int32_t* d_chunk_type, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (n == 0) return DCB_OK;
+  if (!d_in || !d_chunk_min || (want_medium && (!d_chunk_medium || !d_chunk_type))) return DCB_EINVAL;
+  StatsArgs s;
+  s.in = d_in; s.n = n; s.chunk = single_chunk(n, chunk) ? n : chunk;
+  s.want_medium = want_medium; s.subtract_min = 1;
+  s.cmin = d_chunk_min; s.cmed = d_chunk_medium; s.ctype = d_chunk_type;
+  dcb_stats_kernel<<<(unsigned)dcb_num_chunks(n, chunk), 256, 0, (cudaStream_t)stream>>>(s);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+
+extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chunk, double eb, uint32_t flags,
+                            int fixed_type, uint32_t fixed_mask17, uint8_t* d_stream, uint64_t capacity,
+                            uint64_t* d_offsets, float* d_cmin, float* d_cmed, int32_t* d_ctype, uint32_t* d_ccrc,
+                            void* d_ws, uint64_t ws_bytes, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int bct = base_ct(ct, &flags);
+  EncArgs a;
+  memset(&a, 0, sizeof a);
+  if (bct < 0 || make_const(eb, &a.k) != DCB_OK || !d_offsets) return DCB_EINVAL;
+  if (n == 0) { CK(cudaMemsetAsync(d_offsets, 0, sizeof(uint64_t), st)); return DCB_OK; }
+  const bool single = single_chunk(n, chunk);
+  if (!single && (chunk % DCB_TILE) != 0) return DCB_EINVAL;
+  if (!d_in || !d_stream || ((uintptr_t)d_stream & 15) || ((uintptr_t)d_in & 3)) return DCB_EINVAL;
+  if (n >= (1ull << 40) || (!single && chunk >= (1ull << 32))) return DCB_EINVAL;
+  const uint64_t K = dcb_num_chunks(n, chunk);
+  const bool per_chunk_mask = (bct == CT_MASK) && !(flags & DCB_F_FIXED_MASK);
+  if ((flags & DCB_F_SUBTRACT_MIN) && !d_cmin) return DCB_EINVAL;
+  if (per_chunk_mask && (!d_cmed || !d_ctype)) return DCB_EINVAL;
+  if ((flags & DCB_F_FIXED_MASK) && (fixed_type < 0 || fixed_type > 7 || fixed_mask17 >= (1u << 17))) return DCB_EINVAL;
+  if ((flags & DCB_F_CRC) && !d_ccrc) return DCB_EINVAL;
+  if (capacity < dcb_max_stream_bytes(n, chunk)) return DCB_ECAPACITY;
+  if (!d_ws || ws_bytes < dcb_workspace_bytes(n, chunk)) return DCB_ECAPACITY;
+
+  a.in = d_in; a.n = n;
+  a.chunk = single ? n : chunk;
+  a.num_tiles = (uint32_t)num_tiles(n);
+  a.tiles_per_chunk = single ? 0u : (uint32_t)(chunk / DCB_TILE);
+  a.flags = flags & 7u;
+  a.fixed_type = fixed_type; a.fixed_mask17 = fixed_mask17;
+  a.out = d_stream; a.offsets = d_offsets; a.cmin = d_cmin; a.cmed = d_cmed; a.ctype = d_ctype;
+  a.ticket = (unsigned int*)d_ws;
+  a.status = (unsigned long long*)((char*)d_ws + 256);
+  if (((uintptr_t)d_in & 15) == 0) a.flags |= DCB_ENC_IN_ALIGNED;
+
+  // a chunk is "one tile" when every chunk fits a single thread block: min / medium are fused in the encoder
+  const bool chunk_is_tile = (a.tiles_per_chunk == 1) || (a.num_tiles == 1);
+  if (!chunk_is_tile) {
+    // tile boundaries inside a chunk fall on arbitrary BITS: boundary words are OR-ed into a zeroed stream
+    a.flags |= DCB_ENC_ATOMIC_OUT;
+    CK(cudaMemsetAsync(d_stream, 0, (size_t)(4 * n + 16), st));
+    if ((flags & DCB_F_SUBTRACT_MIN) || per_chunk_mask) {
+      StatsArgs s;
+      s.in = d_in; s.n = n; s.chunk = a.chunk; s.want_medium = per_chunk_mask ? 1 : 0;
+      s.subtract_min = (flags & DCB_F_SUBTRACT_MIN) ? 1 : 0;
+      s.cmin = d_cmin; s.cmed = d_cmed; s.ctype = d_ctype;
+      dcb_stats_kernel<<<(unsigned)K, 256, 0, st>>>(s);
+      CK(cudaGetLastError());
+      a.flags |= DCB_ENC_STATS_READY;
+    }
+  }
+  CK(cudaMemsetAsync(d_ws, 0, (size_t)dcb_workspace_bytes(n, chunk), st));
+  cudaError_t e;
+  switch (bct) {
+    case CT_BITWISE: e = launch_encode<CT_BITWISE>(a, st); break;
+    case CT_NP: e = launch_encode<CT_NP>(a, st); break;
+    case CT_MASK: e = launch_encode<CT_MASK>(a, st); break;
+    default: e = launch_encode<CT_OP>(a, st); break;
+  }
+  CK(e);
+  if (flags & DCB_F_CRC) {
+    dcb_crc_kernel<<<(unsigned)((K + 3) / 4), 128, 0, st>>>(d_stream, d_offsets, K, d_ccrc);
+    CK(cudaGetLastError());
+  }
+  return DCB_OK;
+}
+
+template <int CT>
+static cudaError_t launch_decode(const DecArgs& a, cudaStream_t st) {
+  const uint64_t per_block = (uint64_t)DEC_WARPS * 32;
+  dcb_decode_kernel<CT><<<(unsigned)((a.num_chunks + per_block - 1) / per_block), DEC_WARPS * 32, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+extern "C" int dcb_decompress(int ct, const uint8_t* d_stream, const uint64_t* d_offsets, uint64_t n, uint64_t chunk,
+                              double eb, uint32_t flags, int fixed_type, uint32_t fixed_mask17,
+                              const float* d_cmin, const float* d_cmed, const int32_t* d_ctype, float* d_out,
+                              int32_t* d_status, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int bct = base_ct(ct, &flags);
+  DecArgs a;
+  memset(&a, 0, sizeof a);
+  if (bct < 0 || make_const(eb, &a.k) != DCB_OK) return DCB_EINVAL;
+  if (d_status) CK(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
+  if (n == 0) return DCB_OK;
+  const bool single = single_chunk(n, chunk);
+  if (!single && (chunk % DCB_TILE) != 0) return DCB_EINVAL;
+  if (!d_stream || !d_offsets || !d_out || ((uintptr_t)d_stream & 3)) return DCB_EINVAL;
+  if (n >= (1ull << 32) && single) return DCB_EINVAL;
+  const bool per_chunk_mask = (bct == CT_MASK) && !(flags & DCB_F_FIXED_MASK);
+  if ((flags & DCB_F_SUBTRACT_MIN) && !d_cmin) return DCB_EINVAL;
+  if (per_chunk_mask && (!d_cmed || !d_ctype)) return DCB_EINVAL;
+  if ((flags & DCB_F_FIXED_MASK) && (fixed_type < 0 || fixed_type > 7 || fixed_mask17 >= (1u << 17))) return DCB_EINVAL;
+  a.stream = d_stream; a.offsets = d_offsets; a.n = n; a.chunk = single ? n : chunk;
+  a.num_chunks = dcb_num_chunks(n, chunk);
+  a.flags = flags & 7u; a.fixed_type = fixed_type; a.fixed_mask17 = fixed_mask17;
+  a.cmin = d_cmin; a.cmed = d_cmed; a.ctype = d_ctype; a.out = d_out; a.status = d_status;
+  cudaError_t e;
+  switch (bct) {
+    case CT_BITWISE: e = launch_decode<CT_BITWISE>(a, st); break;
+    case CT_NP: e = launch_decode<CT_NP>(a, st); break;
+    case CT_MASK: e = launch_decode<CT_MASK>(a, st); break;
+    default: e = launch_decode<CT_OP>(a, st); break;
+  }
+  CK(e);
+  return DCB_OK;
+}
+
+extern "C" int dcb_crc32_chunks(const uint8_t* d_stream, const uint64_t* d_offsets, uint64_t K, uint32_t* d_crc,
+                                void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (K == 0) return DCB_OK;
+  if (!d_stream || !d_offsets || !d_crc) return DCB_EINVAL;
+  dcb_crc_kernel<<<(unsigned)((K + 3) / 4), 128, 0, (cudaStream_t)stream>>>(d_stream, d_offsets, K, d_crc);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+
+extern "C" int dcb_flip_bits(uint8_t* d_stream, const uint64_t* d_idx, uint64_t count, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (count == 0) return DCB_OK;
+  if (!d_stream || !d_idx || ((uintptr_t)d_stream & 3)) return DCB_EINVAL;
+  dcb_flip_kernel<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_stream, d_idx, count);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+
+// ---- host-pointer layer: cached device buffers (grow only), one stream ---------------------------------------
+struct HostCtx {
+  cudaStream_t st = nullptr;
+  void* buf[8] = {nullptr};
+  size_t cap[8] = {0};
+};
+static thread_local HostCtx g_h;
+static int hbuf(int i, size_t bytes, void** p) {
+  bytes = (bytes + 255) & ~(size_t)255;
+  if (bytes == 0) bytes = 256;
+  if (g_h.cap[i] < bytes) {
+    if (g_h.buf[i]) cudaFree(g_h.buf[i]);
+    g_h.buf[i] = nullptr; g_h.cap[i] = 0;
+    CK(cudaMalloc(&g_h.buf[i], bytes));
+    g_h.cap[i] = bytes;
+  }
+  *p = g_h.buf[i];
+  return DCB_OK;
+}
+#define HB(i, bytes, ptr) do { int rc_ = hbuf(i, bytes, (void**)&(ptr)); if (rc_) return rc_; } while (0)
+
+extern "C" int dcb_compress_host(int ct, const float* h_in, uint64_t n, uint64_t chunk, double eb, uint32_t flags,
+                                 int fixed_type, uint32_t fixed_mask17, uint8_t* h_stream, uint64_t* h_offsets,
+                                 float* h_cmin, float* h_cmed, int32_t* h_ctype, uint32_t* h_ccrc) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (!h_offsets) return DCB_EINVAL;
+  if (n == 0) { h_offsets[0] = 0; return DCB_OK; }
+  if (!h_in || !h_stream) return DCB_EINVAL;
+  if (!g_h.st) CK(cudaStreamCreateWithFlags(&g_h.st, cudaStreamNonBlocking));
+  cudaStream_t st = g_h.st;
+  const uint64_t K = dcb_num_chunks(n, chunk);
+  float* d_in; uint8_t* d_s; uint64_t* d_off; float* d_min; float* d_med; int32_t* d_ty; uint32_t* d_crc; void* d_ws;
+  HB(0, n * 4, d_in); HB(1, dcb_max_stream_bytes(n, chunk), d_s); HB(2, (K + 1) * 8, d_off);
+  HB(3, K * 4, d_min); HB(4, K * 4, d_med); HB(5, K * 4, d_ty); HB(6, K * 4, d_crc);
+  HB(7, dcb_workspace_bytes(n, chunk), d_ws);
+  CK(cudaMemcpyAsync(d_in, h_in, n * 4, cudaMemcpyHostToDevice, st));
+  uint32_t f2 = flags;
+  const int bct = base_ct(ct, &f2);
+  int rc = dcb_compress(ct, d_in, n, chunk, eb, flags, fixed_type, fixed_mask17, d_s, dcb_max_stream_bytes(n, chunk),
+                        d_off, d_min, d_med, d_ty, d_crc, d_ws, dcb_workspace_bytes(n, chunk), st);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(h_offsets, d_off, (K + 1) * 8, cudaMemcpyDeviceToHost, st));
+  if (h_cmin) CK(cudaMemcpyAsync(h_cmin, d_min, K * 4, cudaMemcpyDeviceToHost, st));
+  if (bct == CT_MASK && !(flags & DCB_F_FIXED_MASK)) {
+    if (h_cmed) CK(cudaMemcpyAsync(h_cmed, d_med, K * 4, cudaMemcpyDeviceToHost, st));
+    if (h_ctype) CK(cudaMemcpyAsync(h_ctype, d_ty, K * 4, cudaMemcpyDeviceToHost, st));
+  }
+  if ((f2 & DCB_F_CRC) && h_ccrc) CK(cudaMemcpyAsync(h_ccrc, d_crc, K * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));                       // the stream length is only known now
+  const uint64_t total = h_offsets[K];
+  if (total) CK(cudaMemcpyAsync(h_stream, d_s, total, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return DCB_OK;
+}
+
+extern "C" int dcb_decompress_host(int ct, const uint8_t* h_stream, const uint64_t* h_offsets, uint64_t n,
+                                   uint64_t chunk, double eb, uint32_t flags, int fixed_type, uint32_t fixed_mask17,
+                                   const float* h_cmin, const float* h_cmed, const int32_t* h_ctype, float* h_out) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (n == 0) return DCB_OK;
+  if (!h_stream || !h_offsets || !h_out) return DCB_EINVAL;
+  if (!g_h.st) CK(cudaStreamCreateWithFlags(&g_h.st, cudaStreamNonBlocking));
+  cudaStream_t st = g_h.st;
+  const uint64_t K = dcb_num_chunks(n, chunk);
+  const uint64_t total = h_offsets[K];
+  if (total > 4 * n + 16) return DCB_EINVAL;
+  float* d_out; uint8_t* d_s; uint64_t* d_off; float* d_min; float* d_med; int32_t* d_ty; int32_t* d_status; 
+  HB(0, n * 4, d_out); HB(1, dcb_max_stream_bytes(n, chunk), d_s); HB(2, (K + 1) * 8, d_off);
+  HB(3, K * 4, d_min); HB(4, K * 4, d_med); HB(5, K * 4, d_ty); HB(6, 256, d_status);
+  CK(cudaMemcpyAsync(d_s, h_stream, total, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(d_off, h_offsets, (K + 1) * 8, cudaMemcpyHostToDevice, st));
+  if (h_cmin) CK(cudaMemcpyAsync(d_min, h_cmin, K * 4, cudaMemcpyHostToDevice, st));
+  if (h_cmed) CK(cudaMemcpyAsync(d_med, h_cmed, K * 4, cudaMemcpyHostToDevice, st));
+  if (h_ctype) CK(cudaMemcpyAsync(d_ty, h_ctype, K * 4, cudaMemcpyHostToDevice, st));
+  int rc = dcb_decompress(ct, d_s, d_off, n, chunk, eb, flags, fixed_type, fixed_mask17,
+                          h_cmin ? d_min : nullptr, h_cmed ? d_med : nullptr, h_ctype ? d_ty : nullptr,
+                          d_out, d_status, st);
+  if (rc) return rc;
+  int32_t status = 0;
+  CK(cudaMemcpyAsync(h_out, d_out, n * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&status, d_status, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return status ? DCB_EFORMAT : DCB_OK;
+}

@@ -1,0 +1,106 @@
+/* dc_b200.h -- C ABI of the B200-native float32 bit-wise codec (libdcb200.so).
+ *
+ * Drop-in boundary for the per-element lossy float compression hot path of
+ * smallcat9603/data-compression, impl/dataCompression.c (CT=5, 6, 11, 7 and the CRC-protected
+ * CT=8/9).  Plain pointers and sizes only; no torch / CUDA types in the signatures (a CUDA stream
+ * is passed as void*, NULL = the legacy default stream).
+ *
+ * Two layers:
+ *   (1) dcb_*  : device-resident, chunked, 64-bit-sized entry points.  One CHUNK == one call of the
+ *               reference routine myCompress_bitwise*(chunk, n, (NULL,0,8)): the history restarts and the
+ *               stream is byte aligned at every chunk boundary.  The byte stream of every chunk is
+ *               bit-identical to the reference's; the chunk table (offsets / min / medium / type / crc)
+ *               lives beside the stream, never inside it.
+ *   (2) the reference's own symbols (dataCompression.h:67-99, 125-143) with unchanged signatures and
+ *               host pointers, declared in dataCompression_b200.h; thin wrappers over (1).
+ *
+ * Every function returns DCB_OK (0) or a negative DCB_E* code; nothing exits the process.
+ */
+#ifndef DC_B200_H
+#define DC_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* compress types: impl/dataCompression.h:10-23 */
+#define DCB_CT_BITWISE      5   /* myCompress_bitwise       dataCompression.c:3310 */
+#define DCB_CT_BITWISE_NP   6   /* myCompress_bitwise_np    :2645 */
+#define DCB_CT_BITWISE_MASK 7   /* myCompress_bitwise_mask  :2030 */
+#define DCB_CT_BITWISE_CRC  8   /* CT=5 stream + do_crc32   impl/pingpong.c:260-274 */
+#define DCB_CT_MASK_CRC     9   /* CT=7 stream + do_crc32   impl/pingpong.c:275-289 */
+#define DCB_CT_BITWISE_OP  11   /* myCompress_bitwise_op    :577 */
+
+/* flags */
+#define DCB_F_SUBTRACT_MIN 1u   /* fuse toSmallDataset_float (:3543) per chunk on compress; add min back on decompress (impl/pingpong.c:562) */
+#define DCB_F_FIXED_MASK   2u   /* CT=7/9: use (fixed_type, fixed_mask17) for every chunk instead of med_dataset_float (:3593) per chunk */
+#define DCB_F_CRC          4u   /* also write do_crc32 (:5524) of every chunk's stream (implied by CT=8/9) */
+
+#define DCB_OK            0
+#define DCB_EINVAL       -1     /* bad argument (ct, error bound, alignment, chunk size) */
+#define DCB_ECAPACITY    -2     /* output / workspace too small */
+#define DCB_ECUDA        -3     /* CUDA runtime error (dcb_last_cuda_error()) */
+#define DCB_ENODEVICE    -4     /* no CUDA device: there is no CPU fallback */
+#define DCB_EFORMAT      -5     /* malformed stream (CT=6 code with leading 1, dataCompression.c:2501) */
+
+#define DCB_TILE_ELEMS 4096u    /* elements one thread block encodes per step */
+
+const char* dcb_version(void);
+const char* dcb_last_cuda_error(void);
+int      dcb_device_count(void);
+
+/* to_absErrorBound_binary (dataCompression.c:5512): smallest n in [0,99] with eb >= 2^-n, else -1 */
+int      dcb_n_eb(double abs_error_bound);
+/* chunk_elems must be 0 (one chunk = whole array, the legacy call) or a multiple of DCB_TILE_ELEMS */
+uint64_t dcb_num_chunks(uint64_t n, uint64_t chunk_elems);
+/* worst case of the stream: every code is <= 32 bits */
+uint64_t dcb_max_stream_bytes(uint64_t n, uint64_t chunk_elems);
+uint64_t dcb_workspace_bytes(uint64_t n, uint64_t chunk_elems);
+
+/* Compress n float32 at d_in (device) into d_stream (device, 16-byte aligned, capacity >= dcb_max_stream_bytes).
+ *   d_chunk_offsets[K+1] : byte offset of every chunk's stream; [K] = total bytes          (always written)
+ *   d_chunk_min[K]       : per-chunk minimum           (required with DCB_F_SUBTRACT_MIN, else may be NULL)
+ *   d_chunk_medium[K], d_chunk_type[K] : med_dataset_float results (CT=7/9 without DCB_F_FIXED_MASK)
+ *   d_chunk_crc[K]       : CRC-32 of every chunk's stream                     (CT=8/9 or DCB_F_CRC)
+ * Asynchronous on cuda_stream. */
+int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chunk_elems, double abs_error_bound,
+                 uint32_t flags, int fixed_type, uint32_t fixed_mask17,
+                 uint8_t* d_stream, uint64_t stream_capacity, uint64_t* d_chunk_offsets,
+                 float* d_chunk_min, float* d_chunk_medium, int32_t* d_chunk_type, uint32_t* d_chunk_crc,
+                 void* d_workspace, uint64_t workspace_bytes, void* cuda_stream);
+
+/* Mirror of dcb_compress: decodes exactly n values (chunk c holds min(chunk_elems, n - c*chunk_elems)).
+ * d_stream must be readable up to the next multiple of 4 bytes past d_chunk_offsets[K].
+ * d_status (device int32, may be NULL) receives DCB_OK / DCB_EFORMAT. */
+int dcb_decompress(int ct, const uint8_t* d_stream, const uint64_t* d_chunk_offsets, uint64_t n,
+                   uint64_t chunk_elems, double abs_error_bound, uint32_t flags, int fixed_type,
+                   uint32_t fixed_mask17, const float* d_chunk_min, const float* d_chunk_medium,
+                   const int32_t* d_chunk_type, float* d_out, int32_t* d_status, void* cuda_stream);
+
+/* do_crc32 (dataCompression.c:5524) of each chunk's stream, as a stand-alone pass */
+int dcb_crc32_chunks(const uint8_t* d_stream, const uint64_t* d_chunk_offsets, uint64_t num_chunks,
+                     uint32_t* d_chunk_crc, void* cuda_stream);
+
+/* toSmallDataset_float (:3543) and med_dataset_float (:3593) on device, one result per chunk */
+int dcb_chunk_stats(const float* d_in, uint64_t n, uint64_t chunk_elems, int want_medium,
+                    float* d_chunk_min, float* d_chunk_medium, int32_t* d_chunk_type, void* cuda_stream);
+
+/* bit_flip (dataCompression.c:5858) test hook: flips bit (7 - bit_index%8) of byte bit_index/8 for each index */
+int dcb_flip_bits(uint8_t* d_stream, const uint64_t* d_bit_indices, uint64_t count, void* cuda_stream);
+
+/* ---- host-pointer convenience (what the legacy symbols and the end-to-end bench call) ----------------
+ * Pinned staging + H2D + kernels + D2H inside.  h_stream needs dcb_max_stream_bytes(); tables need K(+1). */
+int dcb_compress_host(int ct, const float* h_in, uint64_t n, uint64_t chunk_elems, double abs_error_bound,
+                      uint32_t flags, int fixed_type, uint32_t fixed_mask17,
+                      uint8_t* h_stream, uint64_t* h_chunk_offsets, float* h_chunk_min, float* h_chunk_medium,
+                      int32_t* h_chunk_type, uint32_t* h_chunk_crc);
+int dcb_decompress_host(int ct, const uint8_t* h_stream, const uint64_t* h_chunk_offsets, uint64_t n,
+                        uint64_t chunk_elems, double abs_error_bound, uint32_t flags, int fixed_type,
+                        uint32_t fixed_mask17, const float* h_chunk_min, const float* h_chunk_medium,
+                        const int32_t* h_chunk_type, float* h_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

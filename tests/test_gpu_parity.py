@@ -1,0 +1,225 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (data_compression_b200.api -> libdcb200.so),
+against the CPU oracle on the same seeded inputs, bit for bit: stream bytes, chunk table, decoded floats.
+Run on the B200 box with  python -m pytest tests -m gpu."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from data_compression_b200 import api
+from data_compression_b200.fields import make_field
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+EBS = (0.1, 0.01, 1e-4, 1e-6)
+CTS = (5, 6, 7, 11)
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.fail("no CUDA device: the product has no CPU fallback and these tests need a B200")
+    return torch.device("cuda:0")
+
+
+def gpu_encode(x, ct, eb, chunk, dev, subtract_min=True, crc=True, fixed=None):
+    xd = torch.from_numpy(np.ascontiguousarray(x)).to(dev)
+    kw = {}
+    if fixed is not None:
+        kw = dict(fixed_type=fixed[0], fixed_mask17=fixed[1])
+    comp = api.compress(xd, ct=ct, abs_error_bound=eb, chunk_elems=chunk, subtract_min=subtract_min, crc=crc, **kw)
+    torch.cuda.synchronize()
+    return comp
+
+
+def assert_same_as_oracle(x, ct, eb, chunk, dev, subtract_min=True, fixed=None, decode=True, tag=""):
+    n = x.size
+    comp = gpu_encode(x, ct, eb, chunk, dev, subtract_min=subtract_min, fixed=fixed)
+    ochunk = chunk if (chunk and chunk < n) else max(n, 1)
+    ft, fm = (fixed if fixed is not None else (-1, 0))
+    enc = ol.o_compress_chunked(ct, x, ochunk, eb, subtract_min=subtract_min, fixed_type=ft, fixed_mask17=fm,
+                                want_crc=True)
+    K = len(enc["offsets"]) - 1
+    offs = comp.chunk_offsets.cpu().numpy().astype(np.uint64)
+    assert np.array_equal(offs, enc["offsets"]), (tag, "offsets")
+    total = int(offs[-1])
+    s = comp.stream[:total].cpu().numpy()
+    if not np.array_equal(s, enc["stream"]):
+        bad = np.nonzero(s != enc["stream"])[0]
+        raise AssertionError("%s: stream differs at %d bytes, first at %d (chunk %d)" %
+                             (tag, bad.size, bad[0], np.searchsorted(offs, bad[0], side="right") - 1))
+    if subtract_min:
+        assert np.array_equal(comp.chunk_min[:K].cpu().numpy().view(np.uint32), enc["chunk_min"].view(np.uint32)), tag
+    if ct == 7 and fixed is None:
+        assert np.array_equal(comp.chunk_medium[:K].cpu().numpy().view(np.uint32),
+                              enc["chunk_medium"].view(np.uint32)), (tag, "medium")
+        assert np.array_equal(comp.chunk_type[:K].cpu().numpy(), enc["chunk_type"]), (tag, "type")
+    assert np.array_equal(comp.chunk_crc[:K].cpu().numpy().view(np.uint32), enc["chunk_crc"]), (tag, "crc")
+    if decode:
+        d = api.decompress(comp).cpu().numpy()
+        od = ol.o_decompress_chunked(ct, enc, n, ochunk, eb, add_min=subtract_min, fixed_type=ft, fixed_mask17=fm)
+        assert np.array_equal(d.view(np.uint32), od.view(np.uint32)), (tag, "decoded")
+    return comp
+
+
+@pytest.mark.parametrize("kind", ("smooth", "noisy", "constant"))
+@pytest.mark.parametrize("ct", CTS)
+def test_fields_chunked(kind, ct, dev):
+    for n in (20000, 65536):
+        x = make_field(kind, n)
+        for eb in EBS:
+            assert_same_as_oracle(x, ct, eb, 4096, dev, tag="%s n=%d ct=%d eb=%g" % (kind, n, ct, eb))
+
+
+@pytest.mark.parametrize("ct", CTS)
+def test_single_chunk_legacy_shapes(ct, dev):
+    """chunk_elems=0: the whole array is ONE reference call (pingpong 131,072; a Himeno face 16,641; tiny n)."""
+    rng = np.random.default_rng(5)
+    for n in (1, 2, 3, 4, 5, 17, 100, 4095, 4096, 4097, 16641, 131072):
+        x = (rng.random(n) * 10).astype(np.float32)
+        if n > 1000:
+            x[n // 3: n // 3 + 500] = make_field("smooth", 500)
+        for eb in (0.01, 1e-6):
+            assert_same_as_oracle(x, ct, eb, 0, dev, tag="single n=%d ct=%d eb=%g" % (n, ct, eb))
+
+
+@pytest.mark.parametrize("ct", CTS)
+def test_multi_tile_chunks(ct, dev):
+    rng = np.random.default_rng(6)
+    x = np.concatenate([make_field("smooth", 30000), (rng.random(21000) * 10).astype(np.float32)])
+    for chunk in (8192, 16384):
+        assert_same_as_oracle(x, ct, 1e-3, chunk, dev, tag="chunk=%d ct=%d" % (chunk, ct))
+
+
+@pytest.mark.parametrize("ct", CTS)
+def test_no_min_subtract_and_fixed_mask(ct, dev):
+    rng = np.random.default_rng(8)
+    x = (rng.random(30000) * 7).astype(np.float32)
+    assert_same_as_oracle(x, ct, 0.01, 4096, dev, subtract_min=False, tag="nomin ct=%d" % ct)
+    if ct == 7:
+        fixed = (2, api.mask17_of(np.float32(3.3)))
+        assert_same_as_oracle(x, ct, 0.01, 4096, dev, subtract_min=False, fixed=fixed, tag="fixedmask")
+        assert_same_as_oracle(x, ct, 1e-5, 0, dev, subtract_min=True, fixed=fixed, tag="fixedmask single")
+
+
+@pytest.mark.parametrize("ct", CTS)
+def test_encoder_only_inputs(ct, dev):
+    """Negative values, the -1.0f history sentinel, Inf/NaN, denormals, zeros of both signs:
+    not decodable by the reference format, but the ENCODING is defined and must match bit for bit."""
+    rng = np.random.default_rng(9)
+    n = 12000
+    neg = (rng.random(n) * 8 - 4).astype(np.float32)
+    sent = (rng.random(n) * 3).astype(np.float32)
+    sent[[0, 5, 6, 7, 100, 101, 300, 4095, 4096, 4097, 8191, n - 1]] = -1.0
+    sent2 = np.full(n, -1.0, np.float32)
+    sent2[::7] = 2.5
+    spec = (rng.random(n) * 3).astype(np.float32)
+    spec[10], spec[20], spec[30], spec[5000] = np.inf, np.nan, -np.inf, np.nan
+    den = (rng.random(n).astype(np.float32) * np.float32(1e-40))
+    zer = (rng.random(n) * 2).astype(np.float32)
+    zer[::5] = 0.0
+    zer[3::10] = -0.0
+    fixed = (2, api.mask17_of(np.float32(1.7))) if ct == 7 else None
+    for name, y in (("neg", neg), ("sentinel", sent), ("sentinel2", sent2), ("special", spec), ("denormal", den),
+                    ("zeros", zer)):
+        for chunk in (4096, 0):
+            assert_same_as_oracle(y, ct, 0.01, chunk, dev, subtract_min=False, fixed=fixed, decode=False,
+                                  tag="%s chunk=%d ct=%d" % (name, chunk, ct))
+    # min-subtract corner cases: NaN first, +0/-0 minima
+    nanfirst = spec.copy(); nanfirst[0] = np.nan
+    mz = zer.copy(); mz[0] = 1.0
+    for name, y in (("nanfirst", nanfirst), ("minus-zero-min", mz)):
+        for chunk in (4096, 0):
+            if ct == 7:
+                continue        # medium of NaN data: nothing to pin
+            assert_same_as_oracle(y, ct, 0.01, chunk, dev, subtract_min=True, decode=False,
+                                  tag="%s chunk=%d ct=%d" % (name, chunk, ct))
+
+
+def test_golden_fixtures(dev, golden_dir):
+    """Committed outputs of the UNMODIFIED reference (tests/golden/make_golden.py)."""
+    d = np.load(os.path.join(golden_dir, "datasets.npz"))
+    for row in d["known_answers"]:
+        name, eb, ct = str(row["name"]), float(row["eb"]), int(row["ct"])
+        x = d[name]
+        comp = gpu_encode(x, ct, eb, 0, dev)
+        total = comp.total_bytes()
+        assert total == row["bytes"], (name, eb, ct)
+        assert np.array_equal(comp.stream[:total].cpu().numpy(), d["stream_%s_%g_%d" % (name, eb, ct)])
+        assert np.uint32(comp.chunk_crc[0].item() & 0xFFFFFFFF) == row["crc32"]
+        assert comp.chunk_min[0].item() == row["min"]
+        if ct == 7:
+            assert (comp.chunk_type[0].item(), api.mask17_of(comp.chunk_medium[0].item())) == (row["type"], row["mask17"])
+        key = "decoded_%s_%g_%d" % (name, eb, ct)
+        if key in d:
+            # the reference tools add min back after decoding (tools/mycompress_bitwise_float.c:60)
+            out = api.decompress(comp).cpu().numpy()
+            want = (d[key] + np.float32(row["min"])).astype(np.float32)
+            assert np.array_equal(out.view(np.uint32), want.view(np.uint32)), key
+    g = np.load(os.path.join(golden_dir, "chunked.npz"))
+    for kind in ("smooth", "noisy", "constant"):
+        x = make_field(kind, 20000)
+        for eb in (0.01, 1e-4):
+            for ct in CTS:
+                key = "%s_%g_%d_" % (kind, eb, ct)
+                comp = gpu_encode(x, ct, eb, 4096, dev)
+                assert np.array_equal(comp.chunk_offsets.cpu().numpy().astype(np.uint64), g[key + "offsets"]), key
+                assert np.array_equal(comp.stream[:comp.total_bytes()].cpu().numpy(), g[key + "stream"]), key
+                assert np.array_equal(comp.chunk_crc[:5].cpu().numpy().view(np.uint32), g[key + "chunk_crc"]), key
+                if key + "decoded" in g:
+                    out = api.decompress(comp).cpu().numpy()
+                    assert np.array_equal(out.view(np.uint32), g[key + "decoded"].view(np.uint32)), key
+
+
+def test_host_pointer_layer(dev):
+    rng = np.random.default_rng(11)
+    x = (rng.random(50000) * 10).astype(np.float32)
+    for ct in (5, 7, 8, 9):
+        enc = api.compress_host(x, ct=ct, abs_error_bound=0.01, chunk_elems=4096)
+        base = 5 if ct in (5, 8) else 7
+        o = ol.o_compress_chunked(base, x, 4096, 0.01, want_crc=True)
+        assert np.array_equal(enc["stream"][:enc["total_bytes"]], o["stream"])
+        if ct in (8, 9):
+            assert np.array_equal(enc["chunk_crc"], o["chunk_crc"])
+        out = api.decompress_host(enc)
+        assert np.array_equal(out.view(np.uint32), ol.o_decompress_chunked(base, o, x.size, 4096, 0.01).view(np.uint32))
+
+
+def test_crc_detects_bit_flip(dev):
+    """CT=8 protocol of impl/pingpong.c:363-410: flip bits in the received stream, recompute, compare."""
+    x = make_field("noisy", 40000)
+    comp = gpu_encode(x, 8, 0.01, 4096, dev)
+    before = comp.chunk_crc[:comp.num_chunks].clone()
+    api.flip_bits(comp.stream, [3, 8 * int(comp.chunk_offsets[2].item()) + 5])
+    after = api.crc32_chunks(comp.stream, comp.chunk_offsets)
+    torch.cuda.synchronize()
+    diff = (before != after).cpu().numpy()
+    assert list(np.nonzero(diff)[0]) == [0, 2]
+
+
+def test_malformed_ct6_stream_is_reported(dev):
+    x = make_field("noisy", 8192)
+    comp = gpu_encode(x, 6, 0.01, 4096, dev)
+    api.flip_bits(comp.stream, [0])                      # leading 1: "Error leading bit 1", dataCompression.c:2501
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    api.decompress(comp, status=status)
+    torch.cuda.synchronize()
+    assert status.item() == -5
+
+
+def test_error_bound_and_reference_drift(dev):
+    """north_star (3): |x - x'| <= absErrorBound is a hard gate only for CT=6; CT=5/7/11 predict from ORIGINAL
+    values in the encoder and RECONSTRUCTED values in the decoder, so the reference itself drifts.
+    The drift must be the reference's own: max error equals the oracle's, bit for bit."""
+    for kind in ("smooth", "noisy"):
+        x = make_field(kind, 65536)
+        for eb in (0.01, 1e-4):
+            c6 = gpu_encode(x, 6, eb, 4096, dev)
+            err6 = np.abs(api.decompress(c6).cpu().numpy().astype(np.float64) - x.astype(np.float64)).max()
+            assert err6 <= eb * (1 + 1e-6) + 1e-6 * np.abs(x).max(), (kind, eb, err6)   # +min rounding slack
+            c5 = gpu_encode(x, 5, eb, 4096, dev)
+            d5 = api.decompress(c5).cpu().numpy()
+            o5 = ol.o_decompress_chunked(5, ol.o_compress_chunked(5, x, 4096, eb), x.size, 4096, eb)
+            assert np.abs(d5 - x).max() == np.abs(o5 - x).max()
