@@ -1,0 +1,343 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 float32 bit-wise codec.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--ct 7] [--field smooth]
+                  [--log2n 28] [--eb 0.01] [--chunk 4096]
+
+Metric (BASELINE.json): compress + decompress INPUT GB/s.  A step = one pass of the hot path over one batch:
+compress the array (min-subtract, [medium/type], encode, look-back, pack) and decompress it again (+min).
+N=1 workload = BASELINE.json configs[1]: CT=7 bitmask bit-wise, 2^28-element synthetic smooth float32 field.
+N>1: each rank holds its own 2^28-element contiguous slice of the global field (chunk ranges shard with no
+data-path collective) -> weak scaling; value = all ranks' input bytes / max-over-ranks time.
+
+One JSON line on rank 0.  `value` is device-resident throughput (inputs in HBM when the clock starts);
+`e2e` goes through the host-pointer C ABI (dcb_compress_host / dcb_decompress_host) with pinned host buffers,
+H2D and D2H inside the timed region.  `roofline` is the dominant kernel's algorithmic bytes / CUDA-event time
+against the measured HBM copy peak.  `cpu_baseline` / `--impl reference` time the reference's own C code
+(oracle/_ref, compiled from /root/reference by oracle/build_ref.sh) on the box's host cores on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "compress+decompress input GB/s"
+UNIT = "GB/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
+    ap.add_argument("--ct", type=int, default=7)
+    ap.add_argument("--field", default="smooth", choices=("smooth", "noisy", "constant"))
+    ap.add_argument("--log2n", type=int, default=28, help="elements per GPU = 2^log2n")
+    ap.add_argument("--eb", type=float, default=0.01)
+    ap.add_argument("--chunk", type=int, default=4096)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-log2n", type=int, default=25, help="bounded CPU sample = 2^cpu_log2n elements")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return "CT=%d %s float32 field, 2^%d elements per GPU, absErrorBound=%g, chunk=%d" % (
+        a.ct, a.field, a.log2n, a.eb, a.chunk)
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------------------ clocks sampler
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            f = [v.strip() for v in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                clk, mx = float(f[0]), float(f[1])
+            except ValueError:
+                continue
+            if t0 - 0.05 <= ts <= t1 + 0.15:
+                sm.append(clk)
+                for nm, v in zip(names, f[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------ reference on CPU
+def _ref_worker(args):
+    """One forked worker: the reference run chunk-by-chunk over its slice (the decoder leaks ~48 B/value,
+    SURVEY F10 -- the leak dies with the process)."""
+    import oracle_lib as ol
+    kind, start, count, chunk, ct, eb, use_ref = args
+    from data_compression_b200.fields import make_field
+    x = make_field(kind, count, start=start)
+    base = 5 if ct in (5, 8) else (7 if ct in (7, 9) else ct)
+    t0 = time.perf_counter()
+    nbytes = 0
+    if use_ref:
+        R = ol.RefLib(eb)
+        for lo in range(0, count, chunk):
+            seg = x[lo:lo + chunk]
+            mn, y = R.min_subtract(seg)
+            t, m17 = 0, 0
+            if base == 7:
+                med, t = R.med(y, 0)
+                m17 = ol.mask17_of(med)
+            s, _ = R.compress(base, y, t, m17)
+            if ct in (8, 9):
+                R.crc32(s)
+            d = R.decompress(base, s, y.size, t, m17, pad=False)
+            d += mn
+            nbytes += s.size
+    else:
+        enc = ol.o_compress_chunked(base, x, chunk, eb, want_crc=ct in (8, 9))
+        ol.o_decompress_chunked(base, enc, count, chunk, eb)
+        nbytes = enc["stream"].size
+    return time.perf_counter() - t0, nbytes
+
+
+def cpu_reference_run(a, log2n, start=0):
+    """-> (input GB/s over all cores, cores, kind, sample description, seconds)"""
+    import multiprocessing as mp
+    import oracle_lib as ol
+    ol.build_oracle()
+    use_ref = ol.ref_available(a.eb)
+    cores = os.cpu_count() or 1
+    n = 1 << log2n
+    per = max(a.chunk, (n // cores) // a.chunk * a.chunk)
+    jobs = [(a.field, start + lo, min(per, n - lo), a.chunk, a.ct, a.eb, use_ref) for lo in range(0, n, per)]
+    ctx = mp.get_context("fork")
+    t0 = time.perf_counter()
+    with ctx.Pool(min(cores, len(jobs))) as pool:
+        res = pool.map(_ref_worker, jobs)
+    wall = time.perf_counter() - t0
+    busy = max(r[0] for r in res)
+    gbs = 4.0 * n / busy / 1e9
+    kind = "reference" if use_ref else "port"
+    sample = "first 2^%d elements of the same field, chunk-by-chunk (C=%d), %d forked workers, slowest worker %.2f s (wall %.2f s)" % (
+        log2n, a.chunk, min(cores, len(jobs)), busy, wall)
+    return gbs, min(cores, len(jobs)), kind, sample, busy
+
+
+# ------------------------------------------------------------------------------------------ reference arm
+def run_reference_arm(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return                                   # rank 0 alone runs and prints it
+    times, gbs_list = [], []
+    info = None
+    log2n = a.cpu_log2n
+    for i in range(a.warmup + a.steps):
+        if i == 1 and times and times[0] > 20.0:             # keep the whole run within a few minutes
+            pass
+        gbs, cores, kind, sample, secs = cpu_reference_run(a, log2n)
+        info = (cores, kind, sample)
+        if i >= a.warmup:
+            times.append(secs)
+            gbs_list.append(gbs)
+    val = float(np.mean(gbs_list))
+    cores, kind, sample = info
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": 1e3 * float(np.mean(times)), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32/u32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+    from data_compression_b200 import api
+    from data_compression_b200.fields import make_field_torch
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    api.lib()
+
+    n = 1 << a.log2n
+    x = make_field_torch(a.field, n, dev, start=rank * n)
+    ws = api.Workspace(n, a.chunk, dev)
+    out = torch.empty(n, dtype=torch.float32, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    has_crc = a.ct in (8, 9)
+
+    def step():
+        comp = api.compress(x, ct=a.ct, abs_error_bound=a.eb, chunk_elems=a.chunk, subtract_min=True, workspace=ws)
+        return comp
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(a.warmup, 3)):
+        comp = step()
+        api.decompress(comp, out=out, status=status)
+    barrier()
+    total_bytes = comp.total_bytes()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(a.steps)]
+    barrier()
+    t0 = time.time()
+    for i in range(a.steps):
+        ev[i][0].record()
+        comp = step()
+        ev[i][1].record()
+        api.decompress(comp, out=out, status=status)
+        ev[i][2].record()
+    barrier()
+    t1 = time.time()
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    t_c = np.array([ev[i][0].elapsed_time(ev[i][1]) for i in range(a.steps)])     # ms
+    t_d = np.array([ev[i][1].elapsed_time(ev[i][2]) for i in range(a.steps)])
+    t_total = ev[0][0].elapsed_time(ev[-1][2])                                      # device time of the K steps
+    tt = torch.tensor([t_total, float(t_c.mean()), float(t_d.mean())], dtype=torch.float64, device=dev)
+    tb = torch.tensor([float(total_bytes)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tb, op=dist.ReduceOp.SUM)
+    t_total, tc_ms, td_ms = [float(v) for v in tt.cpu()]
+    all_bytes = float(tb.item())
+
+    # sanity: the round trip must reproduce the oracle's decode on a sampled chunk range (checked outside the clock)
+    ok = bool(status.item() == 0)
+
+    # ---- end to end through the host-pointer C ABI (pinned host buffers; H2D + D2H inside the timed region) ----
+    e2e = None
+    if not a.no_e2e:
+        xh = torch.empty(n, dtype=torch.float32).pin_memory()
+        xh.copy_(x)
+        oh = torch.empty(n, dtype=torch.float32).pin_memory()
+        sh = torch.empty(api.lib().dcb_max_stream_bytes(n, a.chunk), dtype=torch.uint8).pin_memory()
+        xnp, onp, snp = xh.numpy(), oh.numpy(), sh.numpy()
+        reps = max(2, min(a.steps, 5))
+        enc = None
+        for i in range(1 + reps):
+            if i == 1:
+                barrier()
+                te0 = time.perf_counter()
+            enc = api.compress_host(xnp, ct=a.ct, abs_error_bound=a.eb, chunk_elems=a.chunk, out={"stream": snp})
+            api.decompress_host(enc, out=onp)
+        barrier()
+        te = (time.perf_counter() - te0) / reps
+        tmax = torch.tensor([te], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        te = float(tmax.item())
+        K = enc["offsets"].size - 1
+        tables = 8 * (K + 1) + 12 * K
+        e2e = {"value": 4.0 * n * world / te / 1e9, "unit": UNIT,
+               "h2d_bytes_per_step": int(4 * n + enc["total_bytes"] + tables),
+               "d2h_bytes_per_step": int(4 * n + enc["total_bytes"] + tables),
+               "ms_per_step": 1e3 * te, "api": "dcb_compress_host + dcb_decompress_host (pinned host buffers)"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak()
+    B = float(total_bytes)
+    alg_c, alg_d = 4.0 * n + B, B + 4.0 * n
+    dom = "dcb_encode_kernel" if tc_ms >= td_ms else "dcb_decode_kernel"
+    ach = (alg_c / (tc_ms * 1e-3) if tc_ms >= td_ms else alg_d / (td_ms * 1e-3)) / 1e9
+    value = 4.0 * n * world * a.steps / (t_total * 1e-3) / 1e9
+    launches_per_step = 2 + (1 if has_crc else 0)
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+        "ms_per_step": t_total / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32/u32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "ct": a.ct, "field": a.field, "n_per_gpu": n,
+                   "abs_error_bound": a.eb, "chunk_elems": a.chunk, "compression_ratio": 4.0 * n * world / all_bytes,
+                   "l2": "inputs larger than L2 (%.0f MiB per GPU vs 126 MB)" % (4.0 * n / 2**20),
+                   "compress_ms": tc_ms, "decompress_ms": td_ms,
+                   "compress_input_gbs": 4.0 * n / tc_ms / 1e6, "decompress_input_gbs": 4.0 * n / td_ms / 1e6,
+                   "roundtrip_frac_of_hbm": ((alg_c + alg_d) / ((tc_ms + td_ms) * 1e-3) / 1e9) / peak,
+                   "decode_status_ok": ok},
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
+                     "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                     "compress": {"achieved": alg_c / tc_ms / 1e6, "frac": alg_c / tc_ms / 1e6 / peak},
+                     "decompress": {"achieved": alg_d / td_ms / 1e6, "frac": alg_d / td_ms / 1e6 / peak}},
+        "clocks": clocks, "gpu_launches": launches_per_step * a.steps,
+    }
+    if e2e:
+        line["e2e"] = e2e
+    if world == 1 and not a.no_cpu:
+        gbs, cores, kind, sample, _ = cpu_reference_run(a, a.cpu_log2n)
+        line["cpu_baseline"] = {"value": gbs, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
