@@ -163,8 +163,7 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
 
 template <int CT>
 static cudaError_t launch_decode(const DecArgs& a, cudaStream_t st) {
-  const uint64_t per_block = (uint64_t)DEC_WARPS * 32;
-  dcb_decode_kernel<CT><<<(unsigned)((a.num_chunks + per_block - 1) / per_block), DEC_WARPS * 32, 0, st>>>(a);
+  dcb_decode_kernel<CT><<<(unsigned)((a.num_chunks + DEC_NT - 1) / DEC_NT), DEC_NT, 0, st>>>(a);
   return cudaGetLastError();
 }
 
@@ -182,7 +181,7 @@ extern "C" int dcb_decompress(int ct, const uint8_t* d_stream, const uint64_t* d
   if (n == 0) return DCB_OK;
   const bool single = single_chunk(n, chunk);
   if (!single && (chunk % DCB_TILE) != 0) return DCB_EINVAL;
-  if (!d_stream || !d_offsets || !d_out || ((uintptr_t)d_stream & 3)) return DCB_EINVAL;
+  if (!d_stream || !d_offsets || !d_out || ((uintptr_t)d_stream & 15)) return DCB_EINVAL;
   if (n >= (1ull << 32) && single) return DCB_EINVAL;
   const bool per_chunk_mask = (bct == CT_MASK) && !(flags & DCB_F_FIXED_MASK);
   if ((flags & DCB_F_SUBTRACT_MIN) && !d_cmin) return DCB_EINVAL;
