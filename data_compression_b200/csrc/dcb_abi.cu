@@ -74,9 +74,30 @@ extern "C" uint64_t dcb_workspace_bytes(uint64_t n, uint64_t chunk) {
   return 256 + 8 * num_tiles(n);
 }
 
+static int g_num_sms = 0;
+static int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      g_num_sms = n;
+    else
+      g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
+// persistent launch: DCB_ENC_BLOCKS_PER_SM resident blocks per SM pull tiles from the ticket counter
 template <int CT>
 static cudaError_t launch_encode(const EncArgs& a, cudaStream_t st) {
-  dcb_encode_kernel<CT><<<a.num_tiles, DCB_NT, 0, st>>>(a);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(dcb_encode_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  // one block becomes the prefix scanner, the others are workers
+  const unsigned grid = 1u + (unsigned)min((uint64_t)a.num_tiles, (uint64_t)num_sms() * DCB_ENC_BLOCKS_PER_SM - 1u);
+  dcb_encode_kernel<CT><<<grid, DCB_NT, sizeof(EncSmem), st>>>(a);
   return cudaGetLastError();
 }
 
@@ -126,6 +147,8 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
   a.fixed_type = fixed_type; a.fixed_mask17 = fixed_mask17;
   a.out = d_stream; a.offsets = d_offsets; a.cmin = d_cmin; a.cmed = d_cmed; a.ctype = d_ctype;
   a.ticket = (unsigned int*)d_ws;
+  a.scanner_claim = (unsigned int*)((char*)d_ws + 4);
+  a.last_bits = (unsigned long long*)((char*)d_ws + 8);
   a.status = (unsigned long long*)((char*)d_ws + 256);
   if (((uintptr_t)d_in & 15) == 0) a.flags |= DCB_ENC_IN_ALIGNED;
 

@@ -46,6 +46,8 @@ struct EncArgs {
   int32_t* ctype;            // [K]
   unsigned long long* status;  // [num_tiles]
   unsigned int* ticket;
+  unsigned int* scanner_claim;    // 0 -> 1 by the first block that runs: it becomes the prefix scanner
+  unsigned long long* last_bits;  // bit length of the whole stream before the final byte round-up (legacy `pos`)
 };
 
 struct DecArgs {

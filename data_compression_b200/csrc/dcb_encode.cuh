@@ -1,75 +1,71 @@
 // dcb_encode.cuh -- single-pass encoder for CT=5/6/7/11 (replaces myCompress_bitwise{,_np,_mask,_op},
 // dataCompression.c:3310, :2645, :2030, :577, and their per-bit add_bit_to_bytes :5456).
 //
-// One thread block = one TILE of 4096 consecutive elements, 16 per thread (blocked arrangement so a
-// thread can concatenate its own codes in registers).  Steps:
-//   1. 128-bit loads of the thread's 16 floats (+3-element look-back from the neighbouring lane)
-//   2. [fused toSmallDataset_float / med_dataset_float when chunk == tile]
-//   3. per element: zero test, best-of-three predictor on the ORIGINAL history (open loop),
-//      else raw / escape / full word  ->  (code, len<=32)
-//   4. block scan of the per-thread bit counts -> bit offset inside the tile
-//   5. each thread shifts its codes into a 64-bit accumulator and stores finished 32-bit words into the
-//      shared-memory staging buffer; the word straddling two threads is completed with one shuffle
-//   6. decoupled look-back over the per-tile bit counts (chunk ends round up to a byte) -> absolute bit
-//      offset of the tile in the output stream; chunk-end tiles write chunk_offsets[c+1]
-//   7. staged words are funnel-shifted to the output alignment, byte-swapped to the reference's
-//      MSB-first byte order and written as coalesced 32-bit words
+// PERSISTENT, SOFTWARE-PIPELINED kernel: 3 thread blocks per SM stay resident and pull TILES of 4096
+// consecutive elements from a ticket counter (16 elements per thread, blocked, so a thread concatenates its
+// own codes in registers and the 3-element look-back needs no shuffles).  v2 (one tile per block) was
+// latency bound -- ticket atomic, DRAM load, five barriers and the look-back round trip are a serial chain
+// per block and only 4-5 blocks fit an SM -- so every long-latency step is now issued one tile ahead:
+//   * the NEXT tile's 16 KB are fetched with cp.async (16 B per thread x 4) into a padded shared-memory
+//     slot per thread (80-byte pitch: conflict-free 128-bit reads) while the current tile is classified
+//   * the ticket of the tile after next is fetched by thread 0 and parked in shared memory
+//   * the decoupled look-back of tile t is resolved during iteration t+1: its status words are loaded at the
+//     top of the iteration and consumed after the classification, when every predecessor has long published
+// Per tile:
+//   1. [fused toSmallDataset_float / med_dataset_float when the chunk is one tile] one block reduction
+//   2. classification.  FAST tile (every value finite and >= 0, i.e. no -1.0f sentinel, no NaN/Inf):
+//        the 3-bit code of every element is built with static shifts into a 48-bit string; the
+//        fallback code (raw / escape / full word) is only computed in warps that actually contain one.
+//      SLOW tile (anything else): the reference's exact sentinel state machine, element by element.
+//   3. block scan of the per-thread bit counts -> bit offset inside the tile; the tile's aggregate is
+//      published for the look-back at once
+//   4. the PREVIOUS tile is finished: look-back (chunk ends round up to a byte), then its staged words are
+//      funnel-shifted to the output alignment, byte-swapped to the reference's MSB-first byte order and
+//      written as coalesced 32-bit words
+//   5. packing of the current tile into the staging buffer: a warp whose threads all hold sixteen 3-bit
+//      codes places its 48-bit strings with three funnel shifts; other warps run a branch-free shift/flush loop
 #pragma once
 #include "dcb_common.cuh"
 
-// (code, len) of the fallback path for one element
-template <int CT>
-__device__ __forceinline__ void fallback_code(uint32_t u, const CodecConst& k, int type, uint32_t mask17,
-                                              uint32_t& code, int& len) {
-  if (CT == CT_OP) { code = u; len = 32; return; }                       // :689-692 full word
-  const int lr = raw_len(u, k.n_eb_m118);
-  if (CT == CT_MASK) {                                                   // compress_bitwise_float_mask :2143-2284
-    if ((u >> 23) == (mask17 >> 8)) {
-      const int m = lr - 9;
+#define DCB_ENC_STATS_READY 0x100u   // EncArgs.flags: cmin / cmed / ctype were filled by the stats pre-pass
+#define DCB_ENC_ATOMIC_OUT  0x200u   // tile boundaries are not byte aligned: partial words go out with atomicOr
+#define DCB_ENC_IN_ALIGNED  0x400u   // input pointer is 16-byte aligned (128-bit loads)
+
+// ------------------------------------------------------------------------------------------------
+// fallback code of one element, TOP-ALIGNED in 32 bits (stream bit 0 of the code = bit 31), plus its length
+//   CT=5/6 raw code R(x): compress_bitwise_float :3479-3520 -- top 9+m bits of the word, truncation
+//   CT=11: the full word (:689-692);  CT=7: M(x), compress_bitwise_float_mask :2143-2284
+template <int CT, bool NONNEG>
+__device__ __forceinline__ void fallback_top(uint32_t u, const CodecConst& k, int type, uint32_t mask17,
+                                             uint32_t& top, int& len) {
+  if (CT == CT_OP) { top = u; len = 32; return; }
+  const int E = NONNEG ? (int)(u >> 23) : (int)((u >> 23) & 0xFFu);
+  const int sh = min(max(150 - k.n_eb - E, 0), 23);        // 32 - (9 + m),  m = clamp(n_eb + E - 127, 0, 23)
+  top = u & (0xFFFFFFFFu << sh);
+  len = 32 - sh;
+  if (CT == CT_MASK) {
+    if ((u >> 23) == (mask17 >> 8)) {                       // sign + exponent equal the mask's (:2172-2180)
+      const int m = 23 - sh;
       const bool low8 = ((u >> 15) & 0xFFu) == (mask17 & 0xFFu);
-      const int kbits = low8 ? max(m - 8, 0) : m;
+      const int kbits = low8 ? max(m - 8, 0) : m;          // mantissa bits 9..m (:2208-2221) or 1..m (:2222-2266)
       const uint32_t prefix = (((1u << type) - 1u) << 1) | (low8 ? 0u : 1u);   // 0, type x 1, flag
-      const uint32_t pay = (u >> (23 - m)) & ((1u << kbits) - 1u);
-      code = (prefix << kbits) | pay;
-      len = type + 2 + kbits;
-      return;
+      const int hdr = type + 2;
+      // payload = mantissa bits (m-kbits+1 .. m), placed right after the header
+      const uint32_t pay = (u << (9 + m - kbits)) & ~__funnelshift_rc(0xFFFFFFFFu, 0u, kbits);   // top-aligned kbits bits
+      top = (prefix << (32 - hdr)) | (pay >> hdr);
+      len = hdr + kbits;
     }
   }
-  code = (lr == 32) ? u : (u >> (32 - lr));                              // compress_bitwise_float :3505-3514
-  len = lr;
-}
-
-// fast path: history = the three previous inputs, all known not to be the -1.0f sentinel
-template <int CT>
-__device__ __forceinline__ void classify(float x, float b1, float b2, float b3, bool predictable,
-                                         const CodecConst& k, int type, uint32_t mask17,
-                                         uint32_t& code, int& len) {
-  const uint32_t u = f2u(x);
-  if (CT == CT_NP) { fallback_code<CT_NP>(u, k, type, mask17, code, len); return; }
-  const float p2 = pred2(b1, b2);
-  const float p3 = pred3(b1, b2, b3);
-  const float d1 = fabsf(__fsub_rn(b1, x));
-  const float d2 = fabsf(__fsub_rn(p2, x));
-  const float d3 = fabsf(__fsub_rn(p3, x));
-  float dmin = d1; uint32_t sel = 5u;                                    // 'a' 101
-  if (d2 < dmin) { dmin = d2; sel = 6u; }                                // 'b' 110 (strict <, :3373)
-  if (d3 < dmin) { dmin = d3; sel = 7u; }                                // 'c' 111
-  const bool zero = fabsf(x) <= k.tz;                                    // fabs(x) < absErrorBound in double, :3390
-  const bool hit = predictable && (dmin <= k.tp);                        // diff_min <= absErrorBound, :3399
-  uint32_t fc; int fl;
-  fallback_code<CT>(u, k, type, mask17, fc, fl);
-  code = zero ? 4u : (hit ? sel : fc);
-  len = (zero || hit) ? 3 : fl;
 }
 
 // slow path: exact sentinel state machine of the reference, history carried in (b3,b2,b1)
 template <int CT>
 __device__ __forceinline__ void classify_sentinel(float x, float& b3, float& b2, float& b1,
                                                   const CodecConst& k, int type, uint32_t mask17,
-                                                  uint32_t& code, int& len) {
+                                                  uint32_t& top, int& len) {
   const uint32_t u = f2u(x);
-  if (CT == CT_NP) { fallback_code<CT_NP>(u, k, type, mask17, code, len); return; }
-  const bool zero = fabsf(x) <= k.tz;
+  if (CT == CT_NP) { fallback_top<CT_NP, false>(u, k, type, mask17, top, len); return; }
+  const bool zero = fabsf(x) <= k.tz;                                    // fabs(x) < absErrorBound in double, :3390
   bool hit = false; uint32_t sel = 5u;
   if (b3 == -1.0f || b2 == -1.0f || b1 == -1.0f) {                       // :3330
     hist_push(b3, b2, b1, x);
@@ -80,14 +76,14 @@ __device__ __forceinline__ void classify_sentinel(float x, float& b3, float& b2,
     const float d2 = fabsf(__fsub_rn(p2, x));
     const float d3 = fabsf(__fsub_rn(p3, x));
     float dmin = d1;
-    if (d2 < dmin) { dmin = d2; sel = 6u; }
-    if (d3 < dmin) { dmin = d3; sel = 7u; }
-    hit = dmin <= k.tp;
+    if (d2 < dmin) { dmin = d2; sel = 6u; }                              // 'b' 110 (strict <, :3373)
+    if (d3 < dmin) { dmin = d3; sel = 7u; }                              // 'c' 111
+    hit = dmin <= k.tp;                                                  // diff_min <= absErrorBound, :3399
     b3 = b2; b2 = b1; b1 = x;                                            // :3386-3388
   }
-  uint32_t fc; int fl;
-  fallback_code<CT>(u, k, type, mask17, fc, fl);
-  code = zero ? 4u : (hit ? sel : fc);
+  uint32_t ft; int fl;
+  fallback_top<CT, false>(u, k, type, mask17, ft, fl);
+  top = zero ? (4u << 29) : (hit ? (sel << 29) : ft);
   len = (zero || hit) ? 3 : fl;
 }
 
@@ -97,16 +93,19 @@ __device__ __forceinline__ void classify_sentinel(float x, float& b3, float& b2,
 // Walking backwards from tile-1:  open = bits of the visited tiles up to and including the first
 // (stream-order) chunk end among them, tail = everything after that chunk end (already well defined,
 // it starts on a byte boundary).  See DESIGN.md "look-back with chunk ends".
+// `w0` = status[tile-1-lane] as loaded earlier by the caller (stale INVALID entries are simply re-read).
 __device__ __forceinline__ unsigned long long lookback_bits(const volatile unsigned long long* status,
-                                                            uint32_t tile, int lane) {
+                                                            uint32_t tile, int lane, unsigned long long w0) {
   unsigned long long open = 0, tail = 0;
-  bool have_end = false;
+  bool have_end = false, first = true;
   int64_t j0 = (int64_t)tile - 1;                 // nearest predecessor handled by lane 0
   while (true) {
     const int64_t j = j0 - lane;
     // tiles before 0 read as "inclusive prefix 0"; only real tiles can still be INVALID
-    unsigned long long w = (j >= 0) ? status[j] : (ST_INCL << ST_SHIFT);
+    unsigned long long w = first ? w0 : ((j >= 0) ? status[j] : (ST_INCL << ST_SHIFT));
+    first = false;
     while (__any_sync(0xffffffffu, (w >> ST_SHIFT) == ST_INVALID)) {
+      __nanosleep(40);
       if ((w >> ST_SHIFT) == ST_INVALID) w = status[j];
     }
     const unsigned incl_mask = __ballot_sync(0xffffffffu, (w >> ST_SHIFT) == ST_INCL);
@@ -133,322 +132,86 @@ __device__ __forceinline__ unsigned long long lookback_bits(const volatile unsig
   }
 }
 
+
 // ------------------------------------------------------------------------------------------------
+#define DCB_XPITCH 20            // floats per thread slot of the input staging buffer (16 + 4 pad)
+#define DCB_ENC_BLOCKS_PER_SM 3
+
 struct EncSmem {
-  uint32_t W[DCB_TILE + 8];      // W[0] = 0; stream word k of the tile lives at W[1 + k]
-  uint32_t warp_tot[DCB_NT / 32];
-  uint32_t xchg[DCB_NT / 32];
-  float redf[DCB_NT / 32];
-  uint32_t redu[DCB_NT / 32];
-  unsigned long long P;
-  uint32_t tile;
+  float X[2][DCB_NT * DCB_XPITCH];   // double-buffered input tiles, one 80-byte slot per thread
+  uint32_t W[DCB_TILE + 8];          // packed tile: W[0] = 0; stream word k of the tile lives at W[1 + k]
+  float red_mn[2][DCB_NT / 32];      // partials of the block reductions, double buffered (see block_stats)
+  float red_mx[2][DCB_NT / 32];
+  uint32_t red_ua[2][DCB_NT / 32];
+  float red_s[2][DCB_NT / 32];
+  uint32_t warp_tot[2][DCB_NT / 32];
+  uint32_t xchg[DCB_NT / 32];        // tail word of every warp's last lane (completes the next warp's first word)
+  float hx[2][DCB_NT / 32][4];       // last three RAW values of every warp (look-back of the next warp's lane 0)
+  uint32_t tkt[2];                   // prefetched tickets
+  unsigned long long P;              // absolute bit offset of the tile being copied out
+  uint32_t pend_tile, pend_bits, pend_c, pend_last;   // the tile packed in the previous iteration (finished one iteration later)
   float mn, med;
   int type;
+  uint32_t fi;
+  uint32_t role;
 };
 
-__device__ __forceinline__ float block_min(float v, EncSmem& sm, int lane, int warp) {
-  #pragma unroll
-  for (int o = 16; o; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
-  if (lane == 0) sm.redf[warp] = v;
-  __syncthreads();
-  float r = sm.redf[0];
-  #pragma unroll
-  for (int w = 1; w < DCB_NT / 32; w++) r = fminf(r, sm.redf[w]);
-  __syncthreads();
-  return r;
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
 }
-__device__ __forceinline__ float block_max(float v, EncSmem& sm, int lane, int warp) {
-  #pragma unroll
-  for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-  if (lane == 0) sm.redf[warp] = v;
-  __syncthreads();
-  float r = sm.redf[0];
-  #pragma unroll
-  for (int w = 1; w < DCB_NT / 32; w++) r = fmaxf(r, sm.redf[w]);
-  __syncthreads();
-  return r;
-}
-__device__ __forceinline__ uint32_t block_min_u32(uint32_t v, EncSmem& sm, int lane, int warp) {
-  #pragma unroll
-  for (int o = 16; o; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
-  if (lane == 0) sm.redu[warp] = v;
-  __syncthreads();
-  uint32_t r = sm.redu[0];
-  #pragma unroll
-  for (int w = 1; w < DCB_NT / 32; w++) r = min(r, sm.redu[w]);
-  __syncthreads();
-  return r;
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+// Fetch tile `tile` into the staging buffer: each thread brings its own 16 consecutive floats.
+__device__ __forceinline__ void issue_tile_load(const EncArgs& a, uint32_t tile, float* slot, int tid) {
+  const uint64_t my0 = (uint64_t)tile * DCB_TILE + (uint64_t)tid * DCB_E;
+  if (my0 + DCB_E <= a.n && (a.flags & DCB_ENC_IN_ALIGNED)) {
+    const float* g = a.in + my0;
+    #pragma unroll
+    for (int q = 0; q < 4; q++) cp_async16(slot + 4 * q, g + 4 * q);
+  } else {                                            // ragged last tile / unaligned input: plain loads, zero padding
+    #pragma unroll
+    for (int e = 0; e < DCB_E; e++) slot[e] = (my0 + e < a.n) ? __ldg(a.in + my0 + e) : 0.0f;
+  }
 }
 
-#define DCB_ENC_STATS_READY 0x100u   // EncArgs.flags: cmin / cmed / ctype were filled by the stats pre-pass
-#define DCB_ENC_ATOMIC_OUT  0x200u   // tile boundaries are not byte aligned: partial words go out with atomicOr
-#define DCB_ENC_IN_ALIGNED  0x400u   // input pointer is 16-byte aligned (128-bit loads)
-
-template <int CT>
-__global__ void __launch_bounds__(DCB_NT) dcb_encode_kernel(const EncArgs a) {
-  __shared__ __align__(16) EncSmem sm;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) { sm.tile = atomicAdd(a.ticket, 1u); sm.W[0] = 0u; }   // dynamic tile id: look-back only waits on started tiles
+// One barrier: block-wide min, max and "largest |x| word" of the raw tile.  `par` alternates between
+// consecutive calls so that the partial arrays need no trailing barrier.
+__device__ __forceinline__ void block_stats(float& mn, float& mx, uint32_t& ua, EncSmem& sm, int par, int lane, int warp) {
+  #pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    ua = max(ua, __shfl_xor_sync(0xffffffffu, ua, o));
+  }
+  if (lane == 0) { sm.red_mn[par][warp] = mn; sm.red_mx[par][warp] = mx; sm.red_ua[par][warp] = ua; }
   __syncthreads();
-  const uint32_t tile = sm.tile;
-  const uint64_t base = (uint64_t)tile * DCB_TILE;
-
-  // ---- chunk geometry --------------------------------------------------------------------------
-  uint64_t c = 0, chunk_start = 0;
-  bool last_in_chunk = (tile == a.num_tiles - 1);
-  if (a.tiles_per_chunk) {
-    c = tile / a.tiles_per_chunk;
-    chunk_start = c * a.chunk;
-    last_in_chunk = last_in_chunk || ((tile % a.tiles_per_chunk) == a.tiles_per_chunk - 1);
-  }
-  const bool submin = (a.flags & 1u) != 0;            // DCB_F_SUBTRACT_MIN
-  const bool fixed_mask = (a.flags & 2u) != 0;        // DCB_F_FIXED_MASK
-  const bool stats_ready = (a.flags & DCB_ENC_STATS_READY) != 0;
-
-  // ---- 1. load 16 consecutive floats per thread ---------------------------------------------------
-  const uint64_t my0 = base + (uint64_t)tid * DCB_E;
-  const int vcnt = (my0 >= a.n) ? 0 : (int)min((uint64_t)DCB_E, a.n - my0);
-  const uint32_t ci = (uint32_t)min((uint64_t)0xFFFFFFF0u, my0 - chunk_start);  // index in chunk (only compared with 3)
-  float x[DCB_E];
-  if (vcnt == DCB_E && (a.flags & DCB_ENC_IN_ALIGNED)) {
-    const float4* p = reinterpret_cast<const float4*>(a.in + my0);
-    #pragma unroll
-    for (int q = 0; q < 4; q++) {
-      const float4 v = __ldg(p + q);
-      x[4 * q] = v.x; x[4 * q + 1] = v.y; x[4 * q + 2] = v.z; x[4 * q + 3] = v.w;
-    }
-  } else {
-    #pragma unroll
-    for (int e = 0; e < DCB_E; e++) x[e] = (e < vcnt) ? __ldg(a.in + my0 + e) : 0.0f;
-  }
-
-  // ---- 2a. toSmallDataset_float (dataCompression.c:3543-3562), fused when the tile is the whole chunk --
-  float mn = 0.0f;
-  if (submin) {
-    if (!stats_ready) {
-      float lm = __uint_as_float(0x7f800000u);
-      #pragma unroll
-      for (int e = 0; e < DCB_E; e++) if (e < vcnt) lm = fminf(lm, x[e]);        // NaN never wins a '<' (:3550)
-      mn = block_min(lm, sm, lane, warp);
-      if (mn == 0.0f) {
-        // +0 / -0 compare equal: the reference keeps the FIRST minimal element; recover its sign
-        uint32_t fi = 0xFFFFFFFFu;
-        float fz = 0.0f;
-        #pragma unroll
-        for (int e = DCB_E - 1; e >= 0; e--)
-          if (e < vcnt && x[e] == 0.0f) { fi = (uint32_t)tid * DCB_E + e; fz = x[e]; }
-        const uint32_t fmin = block_min_u32(fi, sm, lane, warp);
-        if (fi == fmin) sm.mn = fz;
-        __syncthreads();
-        mn = sm.mn;
-        __syncthreads();
-      }
-      if (tid == 0) { if (x[0] != x[0]) sm.mn = x[0]; else sm.mn = mn; }           // data[0] NaN stays the min
-      __syncthreads();
-      mn = sm.mn;
-      if (tid == 0) a.cmin[c] = mn;
-    } else {
-      mn = a.cmin[c];
-    }
-    #pragma unroll
-    for (int e = 0; e < DCB_E; e++) x[e] = __fsub_rn(x[e], mn);
-  } else if (a.cmin && tid == 0 && last_in_chunk) {
-    a.cmin[c] = 0.0f;
-  }
-
-  // ---- look-back values x[-1], x[-2], x[-3] of the thread's first element ------------------------------
-  float h1 = __shfl_up_sync(0xffffffffu, x[DCB_E - 1], 1);
-  float h2 = __shfl_up_sync(0xffffffffu, x[DCB_E - 2], 1);
-  float h3 = __shfl_up_sync(0xffffffffu, x[DCB_E - 3], 1);
-  if (lane == 0) {
-    h1 = h2 = h3 = 0.0f;
-    if (vcnt > 0 && CT != CT_NP) {
-      if (ci >= 1) h1 = __ldg(a.in + my0 - 1);
-      if (ci >= 2) h2 = __ldg(a.in + my0 - 2);
-      if (ci >= 3) h3 = __ldg(a.in + my0 - 3);
-      if (submin) { h1 = __fsub_rn(h1, mn); h2 = __fsub_rn(h2, mn); h3 = __fsub_rn(h3, mn); }
-    }
-  }
-
-  // ---- 2b. med_dataset_float (:3593-3620): SEQUENTIAL float32 sum (order matters), max -> type -----------
-  int type = a.fixed_type;
-  uint32_t mask17 = a.fixed_mask17;
-  if (CT == CT_MASK && !fixed_mask) {
-    if (!stats_ready) {
-      float* Wf = reinterpret_cast<float*>(sm.W + 4);   // 16-byte aligned alias of the staging buffer
-      #pragma unroll
-      for (int e = 0; e < DCB_E; e++) Wf[tid * DCB_E + e] = x[e];
-      float lmx = __uint_as_float(0xff800000u);
-      #pragma unroll
-      for (int e = 0; e < DCB_E; e++) if (e < vcnt) lmx = fmaxf(lmx, x[e]);
-      const float mx = block_max(lmx, sm, lane, warp);       // (barriers inside also publish Wf)
-      if (tid == 0) {
-        const int cnt = (int)min((uint64_t)DCB_TILE, a.n - base);
-        float total = 0.0f;
-        int i = 0;
-        for (; i + 4 <= cnt; i += 4) {
-          const float4 v = *reinterpret_cast<const float4*>(Wf + i);
-          total = __fadd_rn(total, v.x); total = __fadd_rn(total, v.y);
-          total = __fadd_rn(total, v.z); total = __fadd_rn(total, v.w);
-        }
-        for (; i < cnt; i++) total = __fadd_rn(total, Wf[i]);
-        const float med = __fdiv_rn(total, (float)cnt);
-        const int ty = (Wf[0] != Wf[0]) ? 0 : type_from_max(mx);   // max starts at data[0]: NaN there defeats every '<'
-        sm.med = med; sm.type = ty;
-        a.cmed[c] = med; a.ctype[c] = ty;
-      }
-      __syncthreads();
-      type = sm.type;
-      mask17 = f2u(sm.med) >> 15;
-      __syncthreads();
-    } else {
-      type = a.ctype[c];
-      mask17 = f2u(a.cmed[c]) >> 15;
-    }
-  }
-
-  // ---- 3. classify: (code, len) per element ---------------------------------------------------------
-  uint32_t code[DCB_E];
-  uint32_t lens[DCB_E / 4] = {0u, 0u, 0u, 0u};
-  uint32_t total = 0;
-  bool sentinel = false;
-  if (CT != CT_NP) {
-    #pragma unroll
-    for (int e = 0; e < DCB_E; e++) sentinel |= (e < vcnt) && (x[e] == -1.0f);
-    sentinel |= (vcnt > 0) && ((ci >= 1 && h1 == -1.0f) || (ci >= 2 && h2 == -1.0f) || (ci >= 3 && h3 == -1.0f));
-    sentinel = __syncthreads_or(sentinel);
-  }
-  if (!sentinel) {
-    #pragma unroll
-    for (int e = 0; e < DCB_E; e++) {
-      const float b1 = (e >= 1) ? x[e - 1] : h1;
-      const float b2 = (e >= 2) ? x[e - 2] : ((e == 1) ? h1 : h2);
-      const float b3 = (e >= 3) ? x[e - 3] : ((e == 2) ? h1 : ((e == 1) ? h2 : h3));
-      int len;
-      classify<CT>(x[e], b1, b2, b3, ci + e >= 3u, a.k, type, mask17, code[e], len);
-      if (e >= vcnt) len = 0;
-      lens[e >> 2] |= (uint32_t)len << (8 * (e & 3));
-      total += len;
-    }
-  } else {
-    // -1.0f is the reference's "empty history slot" marker: rebuild the exact state this thread
-    // starts from by walking back over the chunk until three non-sentinel values are found.
-    float b3 = -1.0f, b2 = -1.0f, b1 = -1.0f;
-    if (vcnt > 0) {
-      float n0 = 0.0f, n1 = 0.0f, n2 = 0.0f;     // newest first
-      int found = 0; bool last_sent = false;
-      for (uint64_t idx = my0; idx > chunk_start && found < 3; idx--) {
-        float v = __ldg(a.in + idx - 1);
-        if (submin) v = __fsub_rn(v, mn);
-        if (idx == my0) last_sent = (v == -1.0f);
-        if (v != -1.0f) {
-          if (found == 0) n0 = v; else if (found == 1) n1 = v; else n2 = v;
-          found++;
-        }
-      }
-      if (found == 1) { b3 = n0; }
-      else if (found == 2) { b3 = n1; b2 = n0; }
-      else if (found == 3) {
-        if (!last_sent) { b3 = n2; b2 = n1; b1 = n0; }
-        else { b3 = n1; b2 = n0; b1 = -1.0f; }
-      }
-    }
-    #pragma unroll
-    for (int e = 0; e < DCB_E; e++) {
-      int len = 0; code[e] = 0;
-      if (e < vcnt) classify_sentinel<CT>(x[e], b3, b2, b1, a.k, type, mask17, code[e], len);
-      lens[e >> 2] |= (uint32_t)len << (8 * (e & 3));
-      total += len;
-    }
-  }
-
-  // ---- 4. block scan of the per-thread bit counts ---------------------------------------------------
-  uint32_t incl = total;
+  mn = sm.red_mn[par][0]; mx = sm.red_mx[par][0]; ua = sm.red_ua[par][0];
   #pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += t;
+  for (int w = 1; w < DCB_NT / 32; w++) {
+    mn = fminf(mn, sm.red_mn[par][w]); mx = fmaxf(mx, sm.red_mx[par][w]); ua = max(ua, sm.red_ua[par][w]);
   }
-  if (lane == 31) sm.warp_tot[warp] = incl;
-  // fast packing needs every thread that has bits to span a 32-bit word boundary (>= 32 bits)
-  const bool fast_pack = __syncthreads_and(total >= 32u || total == 0u);
-  uint32_t warp_base = 0, tile_bits = 0;
+}
+__device__ __forceinline__ float block_sum_any_order(float v, EncSmem& sm, int par, int lane, int warp) {
   #pragma unroll
-  for (int w = 0; w < DCB_NT / 32; w++) {
-    const uint32_t t = sm.warp_tot[w];
-    if (w < warp) warp_base += t;
-    tile_bits += t;
-  }
-  const uint32_t s = warp_base + incl - total;        // first bit of this thread inside the tile
+  for (int o = 16; o; o >>= 1) v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, o));
+  if (lane == 0) sm.red_s[par][warp] = v;
+  __syncthreads();
+  float r = sm.red_s[par][0];
+  #pragma unroll
+  for (int w = 1; w < DCB_NT / 32; w++) r = __fadd_rn(r, sm.red_s[par][w]);
+  return r;
+}
 
-  // ---- 6a. publish the aggregate, then warp 0 looks back while the other warps pack ----------------------
-  volatile unsigned long long* status = a.status;
-  if (warp == 0) {
-    unsigned long long P = 0;
-    if (tile > 0) {
-      if (lane == 0)
-        status[tile] = (ST_AGG << ST_SHIFT) | (last_in_chunk ? ST_END_BIT : 0ull) | (unsigned long long)tile_bits;
-      P = lookback_bits(status, tile, lane);
-    }
-    if (lane == 0) {
-      unsigned long long E = P + tile_bits;
-      if (last_in_chunk) E = (E + 7ull) & ~7ull;
-      status[tile] = (ST_INCL << ST_SHIFT) | E;
-      sm.P = P;
-      if (tile == 0) a.offsets[0] = 0ull;
-      if (last_in_chunk) a.offsets[c + 1] = E >> 3;
-    }
-  }
+// 3-bit field of element e inside the 48-bit string (chi:clo, element 0 at the top)
+#define C48_FIELD(chi, clo, e) ((e) <= 9 ? (((chi) >> (29 - 3 * (e))) & 7u) : \
+                                ((e) == 10 ? ((((chi) << 1) & 6u) | ((clo) >> 31)) : (((clo) >> (61 - 3 * (e))) & 7u)))
 
-  // ---- 5. pack ---------------------------------------------------------------------------------------
-  uint32_t hi = 0, lo = 0;
-  uint32_t fill = s & 31u;
-  uint32_t widx = 1u + (s >> 5);
-  const uint32_t hw = widx;
-  if (fast_pack) {
-    #pragma unroll
-    for (int e = 0; e < DCB_E; e++) {
-      const uint32_t L = (lens[e >> 2] >> (8 * (e & 3))) & 0xFFu;
-      if (L) {
-        const uint32_t cl = code[e] << (32u - L);
-        hi |= cl >> fill;
-        lo = __funnelshift_r(0u, cl, fill);
-        fill += L;
-        if (fill >= 32u) { sm.W[widx++] = hi; hi = lo; lo = 0u; fill -= 32u; }
-      }
-    }
-    // the word straddling two threads is stored by the later one; it ORs in the earlier thread's tail
-    const uint32_t prevT = __shfl_up_sync(0xffffffffu, hi, 1);
-    if (lane > 0 && total > 0u && (s & 31u)) sm.W[hw] |= prevT;
-    if (lane == 31) sm.xchg[warp] = hi;
-    if (total > 0u && s + total == tile_bits) {          // last thread that has bits: flush its tail, zero what follows
-      if (fill) sm.W[widx++] = hi;
-      sm.W[widx] = 0u; sm.W[widx + 1] = 0u;
-    }
-    __syncthreads();
-    if (lane == 0 && warp > 0 && total > 0u && (s & 31u)) sm.W[hw] |= sm.xchg[warp - 1];
-    __syncthreads();
-  } else {
-    // ragged tile (fewer than 11 valid elements in some thread): zero the buffer and OR every word in
-    for (int i = tid; i < DCB_TILE + 8; i += DCB_NT) sm.W[i] = 0u;
-    __syncthreads();
-    #pragma unroll
-    for (int e = 0; e < DCB_E; e++) {
-      const uint32_t L = (lens[e >> 2] >> (8 * (e & 3))) & 0xFFu;
-      if (L) {
-        const uint32_t cl = code[e] << (32u - L);
-        hi |= cl >> fill;
-        lo = __funnelshift_r(0u, cl, fill);
-        fill += L;
-        if (fill >= 32u) { atomicOr(&sm.W[widx++], hi); hi = lo; lo = 0u; fill -= 32u; }
-      }
-    }
-    if (fill && total > 0u) atomicOr(&sm.W[widx], hi);
-    __syncthreads();
-  }
-
-  // ---- 7. copy out: shift to the output bit alignment, MSB-first byte order, coalesced words ---------------
-  const unsigned long long P = sm.P;
+// copy-out: shift the packed tile to the output bit alignment, MSB-first byte order, coalesced 32-bit words
+__device__ __forceinline__ void copy_out_tile(const EncArgs& a, const EncSmem& sm, unsigned long long P,
+                                              uint32_t tile_bits, bool last_in_chunk, int tid) {
   unsigned long long Eabs = P + tile_bits;
   if (last_in_chunk) Eabs = (Eabs + 7ull) & ~7ull;          // zero padding of the chunk's last byte (:5467)
   if (Eabs == P) return;
@@ -476,4 +239,513 @@ __global__ void __launch_bounds__(DCB_NT) dcb_encode_kernel(const EncArgs a) {
       }
     }
   }
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// CENTRAL SCANNER.  A look-back window of 32 tiles advances the inclusive-prefix frontier by at most 32 tiles
+// per L2 round trip, which capped every earlier version at ~45 tiles/us (1.4 ms for 2^28 elements) no matter
+// how cheap the rest was (profiles/r1_v3_summary.md).  Instead the first block that starts running becomes
+// the scanner: it streams over the status array 256 tiles per hop, turns aggregates into inclusive prefixes
+// with a block-wide scan, and writes them back.  A worker needs exactly one word, the inclusive prefix of
+// the tile before its own, one iteration after it published its aggregate.
+//
+// Status word of tile j:  [63:62] state (0 invalid, 1 aggregate, 2 inclusive)  [61] the tile ends a chunk
+//                         [55:0] aggregate: bits of the tile / inclusive: E(j), the absolute bit offset after it
+// E(j) = ends_chunk(j) ? round_up_8(E(j-1) + bits(j)) : E(j-1) + bits(j)        (chunks are byte aligned)
+// The scan operator on (flag, B1, B2a, B2o) -- "no chunk end inside: +B1" or "round_up_8(p + B1) + B2a + B2o",
+// B2a the byte-aligned part after the first chunk end, B2o the open bits after the last one -- is associative.
+struct ScanEl { uint32_t f1; uint32_t a; uint32_t o; };   // f1 = flag << 31 | B1
+__device__ __forceinline__ ScanEl scan_combine(const ScanEl L, const ScanEl R) {   // L earlier in the stream
+  const uint32_t lf = L.f1 >> 31, rf = R.f1 >> 31, lb = L.f1 & 0x7FFFFFFFu, rb = R.f1 & 0x7FFFFFFFu;
+  ScanEl x;
+  if (!rf) {
+    if (!lf) { x.f1 = lb + rb; x.a = 0u; x.o = 0u; }
+    else { x.f1 = L.f1; x.a = L.a; x.o = L.o + rb; }
+  } else {
+    if (!lf) { x.f1 = 0x80000000u | (lb + rb); x.a = R.a; x.o = R.o; }
+    else { x.f1 = L.f1; x.a = L.a + ((L.o + rb + 7u) & ~7u) + R.a; x.o = R.o; }
+  }
+  return x;
+}
+__device__ __forceinline__ unsigned long long scan_apply(unsigned long long p, const ScanEl x) {
+  const unsigned long long b1 = x.f1 & 0x7FFFFFFFu;
+  return (x.f1 >> 31) ? (((p + b1 + 7ull) & ~7ull) + x.a + x.o) : (p + b1);
+}
+
+struct ScanSmem {
+  ScanEl wtot[DCB_NT / 32];
+  uint32_t first_invalid[DCB_NT / 32];
+  unsigned long long P;
+};
+
+__device__ __noinline__ void scanner_role(const EncArgs& a, ScanSmem& ss, int tid) {
+  volatile unsigned long long* status = a.status;
+  const int lane = tid & 31, warp = tid >> 5;
+  const uint32_t limit = a.num_tiles - 1u;             // nobody needs the inclusive prefix of the last tile
+  uint32_t q = 0u;
+  unsigned long long P = 0ull;
+  while (q < limit) {
+    const uint32_t j = q + (uint32_t)tid;
+    unsigned long long w = 0ull;
+    if (j < limit) w = status[j];
+    const bool valid = (w >> ST_SHIFT) != ST_INVALID;
+    const unsigned inval = __ballot_sync(0xffffffffu, !valid);
+    if (lane == 0) ss.first_invalid[warp] = inval ? (uint32_t)(__ffs(inval) - 1) : 32u;
+    ScanEl x;
+    x.f1 = ((w & ST_END_BIT) ? 0x80000000u : 0u) | (uint32_t)(w & 0x7FFFFFFFull);
+    x.a = 0u; x.o = 0u;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      ScanEl y;
+      y.f1 = __shfl_up_sync(0xffffffffu, x.f1, o);
+      y.a = __shfl_up_sync(0xffffffffu, x.a, o);
+      y.o = __shfl_up_sync(0xffffffffu, x.o, o);
+      if (lane >= o) x = scan_combine(y, x);
+    }
+    if (lane == 31) ss.wtot[warp] = x;
+    __syncthreads();
+    uint32_t m = 0u;                                    // leading valid entries of this hop
+    #pragma unroll
+    for (int wq = 0; wq < DCB_NT / 32; wq++) {
+      const uint32_t fi = ss.first_invalid[wq];
+      if (m == 32u * wq) m += fi;
+    }
+    if (m == 0u) { __syncthreads(); __nanosleep(100); continue; }
+    if ((uint32_t)tid < m) {
+      ScanEl pre; pre.f1 = 0u; pre.a = 0u; pre.o = 0u;
+      for (int wq = 0; wq < warp; wq++) pre = scan_combine(pre, ss.wtot[wq]);
+      const ScanEl incl = (warp > 0) ? scan_combine(pre, x) : x;
+      const unsigned long long E = scan_apply(P, incl);
+      status[j] = (ST_INCL << ST_SHIFT) | E;
+      if ((uint32_t)tid == m - 1u) ss.P = E;
+    }
+    __syncthreads();
+    P = ss.P;
+    q += m;
+  }
+}
+
+// thread 0 of a worker: wait for the inclusive prefix of tile-1, publish the chunk offset of the pending tile
+__device__ __forceinline__ void resolve_pending(const EncArgs& a, EncSmem& sm, unsigned long long w0) {
+  volatile unsigned long long* status = a.status;
+  const uint32_t tile = sm.pend_tile;
+  unsigned long long P = 0ull;
+  if (tile > 0u) {
+    while ((w0 >> ST_SHIFT) != ST_INCL) { __nanosleep(20); w0 = status[tile - 1u]; }
+    P = w0 & ST_VAL_MASK;
+  }
+  unsigned long long E = P + sm.pend_bits;
+  if (tile == a.num_tiles - 1u && a.last_bits) *a.last_bits = E;
+  sm.P = P;
+  if (tile == 0u) a.offsets[0] = 0ull;
+  if (sm.pend_last) a.offsets[(uint64_t)sm.pend_c + 1ull] = (E + 7ull) >> 3;
+}
+
+template <int CT>
+__global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kernel(const EncArgs a) {
+  extern __shared__ __align__(16) unsigned char dcb_enc_smem[];
+  EncSmem& sm = *reinterpret_cast<EncSmem*>(dcb_enc_smem);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  volatile unsigned long long* status = a.status;
+  // The first block that starts running becomes the scanner (claimed at run time, so it is resident by
+  // construction); every other block is a worker.  Tile ids are tickets for the same reason: a tile is only
+  // ever claimed by a running block, so nobody waits on an unscheduled one.
+  if (tid == 0) {
+    const uint32_t role = (a.num_tiles > 1u && atomicCAS(a.scanner_claim, 0u, 1u) == 0u) ? 1u : 0u;
+    sm.role = role;
+    if (!role) { sm.tkt[0] = atomicAdd(a.ticket, 1u); sm.tkt[1] = atomicAdd(a.ticket, 1u); }
+    sm.W[0] = 0u;
+  }
+  __syncthreads();
+  if (sm.role) { scanner_role(a, *reinterpret_cast<ScanSmem*>(sm.X[0]), tid); return; }
+  uint32_t cur = sm.tkt[0], nxt = sm.tkt[1];
+  if (cur >= a.num_tiles) return;
+  issue_tile_load(a, cur, &sm.X[0][tid * DCB_XPITCH], tid);
+  cp_async_commit();
+
+  const bool submin = (a.flags & 1u) != 0;            // DCB_F_SUBTRACT_MIN
+  const bool fixed_mask = (a.flags & 2u) != 0;        // DCB_F_FIXED_MASK
+  const bool stats_ready = (a.flags & DCB_ENC_STATS_READY) != 0;
+  const uint32_t abs_mask = submin ? 0x7FFFFFFFu : 0xFFFFFFFFu;   // without min-subtract a negative value makes the tile SLOW
+
+  uint32_t fix_hw = 0; bool fix_need = false;         // lane 0 of warps > 0: first word of the pending tile still lacks the previous warp's tail
+  int par = 0;
+
+  for (uint32_t it = 0;; it++) {
+    const int buf = (int)(it & 1u);
+    float* slot = &sm.X[buf][tid * DCB_XPITCH];
+    // ---- issue everything with a long latency for LATER use -------------------------------------------
+    if (nxt < a.num_tiles) issue_tile_load(a, nxt, &sm.X[buf ^ 1][tid * DCB_XPITCH], tid);
+    cp_async_commit();
+    uint32_t tk = 0u;
+    if (tid == 0) tk = atomicAdd(a.ticket, 1u);                         // ticket of the tile after next
+    unsigned long long w0 = 0ull;                                       // inclusive prefix of the tile before the pending one
+    if (tid == 0 && it > 0u && sm.pend_tile > 0u) w0 = status[sm.pend_tile - 1u];
+    if (fix_need) sm.W[fix_hw] |= sm.xchg[warp - 1];                    // (ordered before the copy-out by the barriers below)
+    fix_need = false;
+
+    // ---- chunk geometry of the current tile ---------------------------------------------------------------
+    const uint32_t tile = cur;
+    const uint64_t base = (uint64_t)tile * DCB_TILE;
+    const bool full = base + DCB_TILE <= a.n;          // block-uniform: no ragged tail in this tile
+    uint32_t c = 0u, tic = 0u;                         // chunk index, tile index inside the chunk
+    bool last_in_chunk = (tile == a.num_tiles - 1);
+    if (a.tiles_per_chunk) {
+      c = tile / a.tiles_per_chunk;
+      tic = tile - c * a.tiles_per_chunk;
+      last_in_chunk = last_in_chunk || (tic == a.tiles_per_chunk - 1);
+    } else {
+      tic = tile;
+    }
+    const uint64_t my0 = base + (uint64_t)tid * DCB_E;
+    const int vcnt = full ? DCB_E : ((my0 >= a.n) ? 0 : (int)min((uint64_t)DCB_E, a.n - my0));
+    const bool first = (tic == 0u && tid == 0);        // chunk start: elements 0..2 have no full history (:3330)
+    float hr1 = 0.0f, hr2 = 0.0f, hr3 = 0.0f;          // RAW look-back values of thread 0 (previous tile of the same chunk)
+    if (tid == 0 && tic > 0u && CT != CT_NP) { hr1 = __ldg(a.in + my0 - 1); hr2 = __ldg(a.in + my0 - 2); hr3 = __ldg(a.in + my0 - 3); }
+
+    // ---- 1. the tile's 16 floats of this thread (landed while the previous tile was processed) ---------------
+    cp_async_wait<1>();
+    float x[DCB_E];
+    #pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const float4 v = *reinterpret_cast<const float4*>(slot + 4 * q);
+      x[4 * q] = v.x; x[4 * q + 1] = v.y; x[4 * q + 2] = v.z; x[4 * q + 3] = v.w;
+    }
+
+    // ---- 2. one block reduction: min (toSmallDataset_float :3543-3562), max (type), largest |x| word (FAST test) --
+    float lmn = __uint_as_float(0x7f800000u), lmx = __uint_as_float(0xff800000u);
+    uint32_t ua = 0u;
+    if (full) {
+      #pragma unroll
+      for (int e = 0; e < DCB_E; e++) { lmn = fminf(lmn, x[e]); lmx = fmaxf(lmx, x[e]); ua = max(ua, f2u(x[e]) & abs_mask); }
+    } else {
+      #pragma unroll
+      for (int e = 0; e < DCB_E; e++) {
+        if (e < vcnt) { lmn = fminf(lmn, x[e]); lmx = fmaxf(lmx, x[e]); }         // NaN never wins a '<' (:3550)
+        ua = max(ua, f2u(x[e]) & abs_mask);                                        // padding is 0.0f
+      }
+    }
+    if (tid == 0) ua = max(ua, max(f2u(hr1) & abs_mask, max(f2u(hr2) & abs_mask, f2u(hr3) & abs_mask)));
+    if (lane == 31) { sm.hx[par][warp][0] = x[DCB_E - 1]; sm.hx[par][warp][1] = x[DCB_E - 2]; sm.hx[par][warp][2] = x[DCB_E - 3]; }
+    block_stats(lmn, lmx, ua, sm, par, lane, warp);
+    float mn = 0.0f;
+    if (submin) mn = stats_ready ? a.cmin[c] : lmn;
+    // FAST tile: every |x| (and |min|) below 2^127, so x - min is finite and >= 0; no NaN/Inf; no negative value
+    // without min-subtract.  Negative values include the -1.0f "empty history slot" sentinel.
+    bool slow = (ua >= 0x7F000000u) || ((f2u(mn) & 0x7FFFFFFFu) >= 0x7F000000u);
+    if (submin && !stats_ready) {
+      if (mn == 0.0f) {
+        // +0 / -0 compare equal: the reference keeps the FIRST minimal element; recover its sign
+        uint32_t fi = 0xFFFFFFFFu;
+        float fz = 0.0f;
+        #pragma unroll
+        for (int e = DCB_E - 1; e >= 0; e--)
+          if (e < vcnt && x[e] == 0.0f) { fi = (uint32_t)tid * DCB_E + e; fz = x[e]; }
+        if (tid == 0) sm.fi = 0xFFFFFFFFu;
+        __syncthreads();
+        atomicMin(&sm.fi, fi);
+        __syncthreads();
+        if (fi == sm.fi && fi != 0xFFFFFFFFu) sm.mn = fz;
+        // x - (+0) keeps a -0.0f input negative: not a FAST tile (the raw code would carry its sign bit)
+        bool negz = false;
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) negz |= (f2u(x[e]) == 0x80000000u);
+        slow = __syncthreads_or(negz) || slow;
+        mn = sm.mn;
+      }
+      if (slow) {                                       // data[0] NaN: every '<' fails and min stays NaN (:3546-3553)
+        __syncthreads();
+        if (tid == 0) sm.mn = (x[0] != x[0]) ? x[0] : mn;
+        __syncthreads();
+        mn = sm.mn;
+      }
+      if (tid == 0) a.cmin[c] = mn;
+    } else if (!submin && a.cmin && tid == 0 && last_in_chunk) {
+      a.cmin[c] = 0.0f;
+    }
+    if (submin) {
+      if (full) {
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) x[e] = __fsub_rn(x[e], mn);
+      } else {
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) x[e] = (e < vcnt) ? __fsub_rn(x[e], mn) : 0.0f;
+      }
+    }
+
+    // ---- look-back values x[-1], x[-2], x[-3] of the thread's first element ------------------------------
+    float h1 = __shfl_up_sync(0xffffffffu, x[DCB_E - 1], 1);
+    float h2 = __shfl_up_sync(0xffffffffu, x[DCB_E - 2], 1);
+    float h3 = __shfl_up_sync(0xffffffffu, x[DCB_E - 3], 1);
+    if (lane == 0) {
+      if (warp > 0) { h1 = sm.hx[par][warp - 1][0]; h2 = sm.hx[par][warp - 1][1]; h3 = sm.hx[par][warp - 1][2]; }
+      else { h1 = hr1; h2 = hr2; h3 = hr3; }
+      if (submin) { h1 = __fsub_rn(h1, mn); h2 = __fsub_rn(h2, mn); h3 = __fsub_rn(h3, mn); }
+    }
+
+    // ---- 2b. med_dataset_float (:3593-3620): SEQUENTIAL float32 sum (order matters), max -> type -----------
+    int type = a.fixed_type;
+    uint32_t mask17 = a.fixed_mask17;
+    if (CT == CT_MASK && !fixed_mask) {
+      if (!stats_ready) {
+        const int cnt = (int)min((uint64_t)DCB_TILE, a.n - base);
+        // Only the top 17 bits of medium reach the stream (mask = first 17 chars of floattostr(medium),
+        // impl/pingpong.c:202-206).  A tree sum S of the non-negative values brackets the reference's
+        // sequential float32 sum:  |S_seq - S| <= (gamma_{cnt-1} + gamma_{32}) * S  (standard forward bound,
+        // u = 2^-24).  If both ends of the bracket give the same 17 bits the mask is decided without the
+        // 4096-step dependent chain; otherwise (and for SLOW tiles) one thread runs the chain exactly.
+        bool decided = false;
+        if (!slow) {
+          float ps = 0.0f;
+          #pragma unroll
+          for (int e = 0; e < DCB_E; e++) ps = __fadd_rn(ps, x[e]);
+          const float S = block_sum_any_order(ps, sm, par, lane, warp);
+          const float rel = (float)(cnt + 64) * (1.02f / 16777216.0f);
+          const float lo = __fmul_rd(S, __fsub_rd(1.0f, rel)), hi = __fmul_ru(S, __fadd_ru(1.0f, rel));
+          const float fc = (float)cnt;
+          const uint32_t mlo = f2u(__fdiv_rn(lo, fc)) >> 15, mhi = f2u(__fdiv_rn(hi, fc)) >> 15;
+          decided = (mlo == mhi) && (f2u(hi) < 0x7F800000u);
+          if (decided) {
+            mask17 = mlo;
+            type = type_from_max(submin ? __fsub_rn(lmx, mn) : lmx);   // max(x - min) == max(x) - min (rounding is monotone)
+            if (tid == 0) { a.cmed[c] = u2f(mask17 << 15); a.ctype[c] = type; }   // only the 17 mask bits are defined
+          }
+        }
+        if (!decided) {                                    // block-uniform
+          #pragma unroll
+          for (int e = 0; e < DCB_E; e++) slot[e] = x[e];  // the consumed input slot doubles as the staging for thread 0
+          float ymx = __uint_as_float(0xff800000u);
+          #pragma unroll
+          for (int e = 0; e < DCB_E; e++) if (e < vcnt) ymx = fmaxf(ymx, x[e]);
+          #pragma unroll
+          for (int o = 16; o; o >>= 1) ymx = fmaxf(ymx, __shfl_xor_sync(0xffffffffu, ymx, o));
+          __syncthreads();
+          if (lane == 0) sm.red_s[par][warp] = ymx;
+          __syncthreads();
+          if (tid == 0) {
+            float mx = sm.red_s[par][0];
+            #pragma unroll
+            for (int w = 1; w < DCB_NT / 32; w++) mx = fmaxf(mx, sm.red_s[par][w]);
+            float total = 0.0f;
+            const float* Y = sm.X[buf];
+            int i = 0;
+            for (; i + DCB_E <= cnt; i += DCB_E) {
+              const float* yp = Y + (i / DCB_E) * DCB_XPITCH;
+              #pragma unroll
+              for (int q = 0; q < 4; q++) {
+                const float4 v = *reinterpret_cast<const float4*>(yp + 4 * q);
+                total = __fadd_rn(total, v.x); total = __fadd_rn(total, v.y);
+                total = __fadd_rn(total, v.z); total = __fadd_rn(total, v.w);
+              }
+            }
+            for (; i < cnt; i++) total = __fadd_rn(total, Y[(i / DCB_E) * DCB_XPITCH + (i % DCB_E)]);
+            const float med = __fdiv_rn(total, (float)cnt);
+            const int ty = (Y[0] != Y[0]) ? 0 : type_from_max(mx);   // max starts at data[0]: NaN there defeats every '<'
+            sm.med = med; sm.type = ty;
+            a.cmed[c] = med; a.ctype[c] = ty;
+          }
+          __syncthreads();
+          type = sm.type;
+          mask17 = f2u(sm.med) >> 15;
+        }
+      } else {
+        type = a.ctype[c];
+        mask17 = f2u(a.cmed[c]) >> 15;
+      }
+    }
+
+    // ---- 3. classify --------------------------------------------------------------------------------------
+    uint32_t code[DCB_E];            // general path: top-aligned codes
+    int len[DCB_E];
+    uint32_t chi = 0u, clo = 0u;     // fast path: sixteen 3-bit fields, element 0 in the top bits of chi (0 = needs a fallback code)
+    uint32_t total = 0;
+    bool all3 = false;               // this thread holds sixteen 3-bit codes (48 bits)
+    if (!slow) {
+      if (CT != CT_NP) {
+        float b1 = h1, b2 = h2, b3 = h3;
+        float t1 = __fmul_rn(3.0f, b1), t2 = __fmul_rn(3.0f, b2);
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) {
+          const float xe = x[e];
+          const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);                 // 2*b1 is exact: == __fmul_rn(2, b1)
+          const float p3 = __fadd_rn(__fsub_rn(t1, t2), b3);
+          const float d1 = fabsf(__fsub_rn(b1, xe));
+          const float d2 = fabsf(__fsub_rn(p2, xe));
+          const float d3 = fabsf(__fsub_rn(p3, xe));
+          const float dmin = fminf(fminf(d1, d2), d3);                       // no NaN/Inf here: plain min == the '<' chain
+          bool hit = dmin <= a.k.tp;                                         // diff_min <= absErrorBound, :3399
+          if (e < 3) hit = hit && !first;
+          const bool zero = xe <= a.k.tz;                                    // fabs(x) < absErrorBound (x >= 0), :3390
+          const uint32_t sel = (d1 == dmin) ? 5u : ((d2 == dmin) ? 6u : 7u);  // first minimum wins == strict '<' updates
+          const uint32_t f = zero ? 4u : (hit ? sel : 0u);
+          if (e <= 9) chi |= f << (29 - 3 * e);
+          else if (e == 10) { chi |= f >> 1; clo |= f << 31; }
+          else clo |= f << (61 - 3 * e);
+          b3 = b2; b2 = b1; b1 = xe;
+          t2 = t1; t1 = __fmul_rn(3.0f, xe);
+        }
+        all3 = (vcnt == DCB_E) && ((chi & 0x92492492u) == 0x92492492u) && ((clo & 0x49240000u) == 0x49240000u);
+      }
+      if (__all_sync(0xffffffffu, all3)) {
+        total = 48u;
+      } else {
+        all3 = false;
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) {
+          const uint32_t f = (CT == CT_NP) ? 0u : C48_FIELD(chi, clo, e);
+          uint32_t ft; int fl;
+          fallback_top<CT, true>(f2u(x[e]), a.k, type, mask17, ft, fl);
+          code[e] = f ? (f << 29) : ft;
+          len[e] = f ? 3 : fl;
+          if (e >= vcnt) { code[e] = 0u; len[e] = 0; }
+          total += (uint32_t)len[e];
+        }
+      }
+    } else {
+      // -1.0f is the reference's "empty history slot" marker: rebuild the exact state this thread
+      // starts from by walking back over the chunk until three non-sentinel values are found.
+      float b3 = -1.0f, b2 = -1.0f, b1 = -1.0f;
+      if (vcnt > 0 && CT != CT_NP) {
+        const uint64_t chunk_start = base - (uint64_t)tic * DCB_TILE;
+        float n0 = 0.0f, n1 = 0.0f, n2 = 0.0f;     // newest first
+        int found = 0; bool last_sent = false;
+        for (uint64_t idx = my0; idx > chunk_start && found < 3; idx--) {
+          float v = __ldg(a.in + idx - 1);
+          if (submin) v = __fsub_rn(v, mn);
+          if (idx == my0) last_sent = (v == -1.0f);
+          if (v != -1.0f) {
+            if (found == 0) n0 = v; else if (found == 1) n1 = v; else n2 = v;
+            found++;
+          }
+        }
+        if (found == 1) { b3 = n0; }
+        else if (found == 2) { b3 = n1; b2 = n0; }
+        else if (found == 3) {
+          if (!last_sent) { b3 = n2; b2 = n1; b1 = n0; }
+          else { b3 = n1; b2 = n0; b1 = -1.0f; }
+        }
+      }
+      #pragma unroll
+      for (int e = 0; e < DCB_E; e++) {
+        len[e] = 0; code[e] = 0u;
+        if (e < vcnt) classify_sentinel<CT>(x[e], b3, b2, b1, a.k, type, mask17, code[e], len[e]);
+        total += (uint32_t)len[e];
+      }
+    }
+
+    // ---- 4. block scan of the per-thread bit counts ---------------------------------------------------
+    uint32_t incl = total;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) sm.warp_tot[par][warp] = incl;
+    // word-owner packing needs every thread that has bits to span a 32-bit word boundary (>= 32 bits)
+    const bool fast_pack = __syncthreads_and(total >= 32u || total == 0u);
+    uint32_t warp_base = 0, tile_bits = 0;
+    #pragma unroll
+    for (int w = 0; w < DCB_NT / 32; w++) {
+      const uint32_t t = sm.warp_tot[par][w];
+      if (w < warp) warp_base += t;
+      tile_bits += t;
+    }
+    const uint32_t s = warp_base + incl - total;        // first bit of this thread inside the tile
+
+    // publish the aggregate at once: the scanner turns it into an inclusive prefix while this block packs.
+    // One tile per chunk: every tile ends byte aligned, so its contribution is simply its bits rounded up to bytes.
+    if (tid == 0) {
+      const bool single = (a.tiles_per_chunk == 1u);
+      const unsigned long long v = single ? (unsigned long long)((tile_bits + 7u) & ~7u) : (unsigned long long)tile_bits;
+      status[tile] = (ST_AGG << ST_SHIFT) | ((last_in_chunk && !single) ? ST_END_BIT : 0ull) | v;
+    }
+
+    // ---- 5. finish the PREVIOUS tile: its start offset (status word loaded at the top), copy-out of the staging buffer ----
+    if (it > 0u) {
+      if (tid == 0) resolve_pending(a, sm, w0);
+      __syncthreads();
+      copy_out_tile(a, sm, sm.P, sm.pend_bits, sm.pend_last != 0u, tid);
+      __syncthreads();
+    }
+
+    // ---- 6. pack the current tile into the staging buffer -------------------------------------------------
+    uint32_t hi = 0u;                                   // on exit: the thread's unfinished last word (its tail)
+    const uint32_t f0 = s & 31u;
+    const uint32_t hw = 1u + (s >> 5);
+    if (fast_pack) {
+      uint32_t widx = hw;
+      if (all3) {
+        // 48-bit string chi:clo placed at bit f0 of word hw: three funnel shifts, at most two finished words
+        const uint32_t w0_ = chi >> f0;
+        const uint32_t w1_ = __funnelshift_r(clo, chi, f0);
+        const uint32_t w2_ = __funnelshift_r(0u, clo, f0);
+        sm.W[hw] = w0_;
+        if (f0 >= 16u) { sm.W[hw + 1] = w1_; hi = w2_; widx = hw + 2; }
+        else { hi = w1_; widx = hw + 1; }
+      } else {
+        uint32_t fill = f0;
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) {
+          const uint32_t cl = code[e];
+          hi |= cl >> fill;
+          const uint32_t lo = __funnelshift_r(0u, cl, fill);
+          fill += (uint32_t)len[e];
+          const bool fl = fill >= 32u;
+          if (fl) sm.W[widx] = hi;
+          widx += fl ? 1u : 0u;
+          hi = fl ? lo : hi;
+          fill &= 31u;
+        }
+      }
+      // the word straddling two threads is stored by the later one; it ORs in the earlier thread's tail
+      const uint32_t prevT = __shfl_up_sync(0xffffffffu, hi, 1);
+      if (lane > 0 && total > 0u && f0) sm.W[hw] |= prevT;
+      if (lane == 31) sm.xchg[warp] = hi;
+      if (total > 0u && s + total == tile_bits) {          // last thread that has bits: flush its tail, zero what follows
+        if ((s + total) & 31u) sm.W[widx++] = hi;
+        sm.W[widx] = 0u; sm.W[widx + 1] = 0u;
+      }
+      fix_need = (lane == 0 && warp > 0 && total > 0u && f0 != 0u);   // completed at the top of the next iteration
+      fix_hw = hw;
+    } else {
+      // ragged tile (fewer than 11 valid elements in some thread): zero the buffer and OR every word in
+      for (int i = tid + 1; i < DCB_TILE + 8; i += DCB_NT) sm.W[i] = 0u;
+      __syncthreads();
+      uint32_t fill = f0, widx = hw;
+      if (all3) {                                          // (cannot happen: all3 implies 48 bits; kept for safety)
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) { code[e] = C48_FIELD(chi, clo, e) << 29; len[e] = 3; }
+      }
+      #pragma unroll
+      for (int e = 0; e < DCB_E; e++) {
+        const uint32_t L = (uint32_t)len[e];
+        if (L) {
+          const uint32_t cl = code[e];
+          hi |= cl >> fill;
+          const uint32_t lo = __funnelshift_r(0u, cl, fill);
+          fill += L;
+          if (fill >= 32u) { atomicOr(&sm.W[widx++], hi); hi = lo; fill -= 32u; }
+        }
+      }
+      if (fill && total > 0u) atomicOr(&sm.W[widx], hi);
+    }
+
+    // ---- 7. rotate the pipeline --------------------------------------------------------------------------
+    if (tid == 0) {
+      sm.pend_tile = tile; sm.pend_bits = tile_bits; sm.pend_c = c; sm.pend_last = last_in_chunk ? 1u : 0u;
+      sm.tkt[buf] = tk;                                  // slot of the ticket just consumed
+    }
+    par ^= 1;
+    cur = nxt;
+    __syncthreads();
+    nxt = sm.tkt[buf];
+    if (cur >= a.num_tiles) break;
+  }
+
+  // ---- epilogue: finish the last tile of this block ---------------------------------------------------------
+  if (fix_need) sm.W[fix_hw] |= sm.xchg[warp - 1];
+  if (tid == 0) resolve_pending(a, sm, 0ull);
+  __syncthreads();
+  copy_out_tile(a, sm, sm.P, sm.pend_bits, sm.pend_last != 0u, tid);
 }
