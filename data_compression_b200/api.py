@@ -27,7 +27,8 @@ ERRORS = {-1: "DCB_EINVAL (bad argument)", -2: "DCB_ECAPACITY (buffer too small)
 
 EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb", "dcb_num_chunks",
            "dcb_max_stream_bytes", "dcb_workspace_bytes", "dcb_compress", "dcb_decompress", "dcb_crc32_chunks",
-           "dcb_chunk_stats", "dcb_flip_bits", "dcb_compress_host", "dcb_decompress_host"]
+           "dcb_chunk_stats", "dcb_chunk_medium", "dcb_flip_bits", "dcb_compress_host", "dcb_decompress_host",
+           "dcb_last_stream_bits"]
 
 _lib = None
 

@@ -115,6 +115,19 @@ extern "C" int dcb_chunk_stats(const float* d_in, uint64_t n, uint64_t chunk, in
   return DCB_OK;
 }
 
+extern "C" int dcb_chunk_medium(const float* d_in, uint64_t n, float* d_medium, int32_t* d_type, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (n == 0) return DCB_OK;
+  if (!d_in || !d_medium || !d_type) return DCB_EINVAL;
+  StatsArgs s;
+  s.in = d_in; s.n = n; s.chunk = n;
+  s.want_medium = 1; s.subtract_min = 0;
+  s.cmin = nullptr; s.cmed = d_medium; s.ctype = d_type;
+  dcb_stats_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(s);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+
 extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chunk, double eb, uint32_t flags,
                             int fixed_type, uint32_t fixed_mask17, uint8_t* d_stream, uint64_t capacity,
                             uint64_t* d_offsets, float* d_cmin, float* d_cmed, int32_t* d_ctype, uint32_t* d_ccrc,
@@ -251,6 +264,8 @@ struct HostCtx {
   size_t cap[8] = {0};
 };
 static thread_local HostCtx g_h;
+static thread_local uint64_t g_last_bits = 0;
+extern "C" uint64_t dcb_last_stream_bits(void) { return g_last_bits; }
 static int hbuf(int i, size_t bytes, void** p) {
   bytes = (bytes + 255) & ~(size_t)255;
   if (bytes == 0) bytes = 256;
@@ -292,6 +307,7 @@ extern "C" int dcb_compress_host(int ct, const float* h_in, uint64_t n, uint64_t
     if (h_ctype) CK(cudaMemcpyAsync(h_ctype, d_ty, K * 4, cudaMemcpyDeviceToHost, st));
   }
   if ((f2 & DCB_F_CRC) && h_ccrc) CK(cudaMemcpyAsync(h_ccrc, d_crc, K * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&g_last_bits, (char*)d_ws + 8, 8, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));                       // the stream length is only known now
   const uint64_t total = h_offsets[K];
   if (total) CK(cudaMemcpyAsync(h_stream, d_s, total, cudaMemcpyDeviceToHost, st));

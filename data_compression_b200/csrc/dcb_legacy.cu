@@ -1,0 +1,202 @@
+// dcb_legacy.cu -- the reference's own float32 hot-path symbols (include/dataCompression_b200.h), as thin
+// host-pointer wrappers over the device API of include/dc_b200.h: ONE chunk = the whole array, exactly one
+// reference call.  Same names, argument meaning, ownership (malloc/realloc'd results the caller owns) and
+// error behaviour (print + exit(1), dataCompression.c:2961-2963) as impl/dataCompression.c.
+// Nothing here encodes or decodes on the CPU: without a CUDA device every codec call exits.
+#include "../../include/dc_b200.h"
+#include "../../include/dataCompression_b200.h"
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+static double g_abs_error_bound = -1.0;           // < 0: not set yet -> environment, then the header default
+
+extern "C" void dc_set_abs_error_bound(double eb) { g_abs_error_bound = eb; }
+extern "C" double dc_get_abs_error_bound(void) {
+  if (g_abs_error_bound < 0.0) {
+    const char* e = getenv("DC_ABS_ERROR_BOUND");
+    g_abs_error_bound = (e && atof(e) > 0.0) ? atof(e) : 0.000001;     // impl/dataCompression.h:5
+  }
+  return g_abs_error_bound;
+}
+
+static void die(const char* what, int rc) {
+  printf("dcb200: %s failed (rc=%d%s%s)\n", what, rc, rc == DCB_ECUDA ? ": " : "", rc == DCB_ECUDA ? dcb_last_cuda_error() : "");
+  exit(1);
+}
+
+// mask[1+8+8] of '0'/'1' chars (impl/pingpong.c:202-206) -> the 17-bit integer the kernels take
+static uint32_t mask17_from_chars(const char* mask) {
+  uint32_t m = 0;
+  for (int i = 0; i < 17; i++) m = (m << 1) | (uint32_t)(mask[i] == '1');
+  return m;
+}
+
+// Appends `nbits` bits (MSB first in src) to the stream (*data_bits, *bytes, *pos) the way repeated
+// add_bit_to_bytes calls would (dataCompression.c:5456-5489).  Every caller in the reference starts from
+// (NULL, 0, 8), for which this is a realloc + memcpy; the shifted merge only runs for a caller-built prefix.
+static void append_stream(unsigned char** data_bits, int* bytes, int* pos, const unsigned char* src, uint64_t nbits) {
+  if (nbits == 0) return;
+  const uint64_t src_bytes = (nbits + 7) / 8;
+  int free_bits = (*pos == 8 || *bytes == 0) ? 0 : *pos;          // unused low bits of the current last byte
+  const uint64_t old_bytes = (uint64_t)*bytes;
+  const uint64_t total_bits = old_bytes * 8 - (uint64_t)free_bits + nbits;
+  const uint64_t new_bytes = (total_bits + 7) / 8;
+  unsigned char* p = (unsigned char*)realloc(*data_bits, (size_t)new_bytes);
+  if (!p) { printf("ERROR: Out of memory\n"); exit(1); }          // dataCompression.c:5473-5477
+  if (free_bits == 0) {
+    memcpy(p + old_bytes, src, (size_t)src_bytes);
+  } else {
+    const int sh = 8 - free_bits;                                  // bits already used in the last byte
+    memset(p + old_bytes, 0, (size_t)(new_bytes - old_bytes));
+    for (uint64_t i = 0; i < src_bytes; i++) {
+      p[old_bytes - 1 + i] |= (unsigned char)(src[i] >> sh);
+      if (old_bytes + i < new_bytes) p[old_bytes + i] |= (unsigned char)(src[i] << free_bits);
+    }
+  }
+  *data_bits = p;
+  *bytes = (int)new_bytes;
+  const int rem = (int)(total_bits % 8);
+  *pos = rem ? 8 - rem : 8;
+}
+
+static void legacy_compress(int ct, float* data, int num, unsigned char** data_bits, int* bytes, int* pos, int type,
+                            const char* mask) {
+  if (num <= 0) return;
+  const uint64_t n = (uint64_t)num;
+  const uint64_t cap = dcb_max_stream_bytes(n, 0);
+  unsigned char* tmp = (unsigned char*)malloc((size_t)cap);
+  if (!tmp) { printf("ERROR: Out of memory\n"); exit(1); }
+  uint64_t offs[2] = {0, 0};
+  uint32_t flags = 0, m17 = 0;
+  if (ct == DCB_CT_BITWISE_MASK) { flags |= DCB_F_FIXED_MASK; m17 = mask17_from_chars(mask); }
+  const int rc = dcb_compress_host(ct, data, n, 0, dc_get_abs_error_bound(), flags, type, m17, tmp, offs, NULL, NULL,
+                                   NULL, NULL);
+  if (rc != DCB_OK) die("dcb_compress_host", rc);
+  append_stream(data_bits, bytes, pos, tmp, dcb_last_stream_bits());
+  free(tmp);
+}
+
+static float* legacy_decompress(int ct, unsigned char* data_bits, int bytes, int num, int type, const char* mask) {
+  float* out = (float*)malloc(sizeof(float) * (size_t)(num > 0 ? num : 1));
+  if (!out) { printf("ERROR: Out of memory\n"); exit(1); }
+  if (num <= 0) return out;
+  uint64_t offs[2] = {0, (uint64_t)(bytes > 0 ? bytes : 0)};
+  uint32_t flags = 0, m17 = 0;
+  if (ct == DCB_CT_BITWISE_MASK) { flags |= DCB_F_FIXED_MASK; m17 = mask17_from_chars(mask); }
+  const int rc = dcb_decompress_host(ct, data_bits, offs, (uint64_t)num, 0, dc_get_abs_error_bound(), flags, type, m17,
+                                     NULL, NULL, NULL, out);
+  if (rc == DCB_EFORMAT) { printf("Error leading bit 1\n"); exit(1); }          // dataCompression.c:2501-2505
+  if (rc != DCB_OK) die("dcb_decompress_host", rc);
+  return out;
+}
+
+extern "C" void myCompress_bitwise(float data[], int num, unsigned char** data_bits, int* bytes, int* pos) {
+  legacy_compress(DCB_CT_BITWISE, data, num, data_bits, bytes, pos, 0, NULL);
+}
+extern "C" float* myDecompress_bitwise(unsigned char* data_bits, int bytes, int num) {
+  return legacy_decompress(DCB_CT_BITWISE, data_bits, bytes, num, 0, NULL);
+}
+extern "C" void myCompress_bitwise_np(float data[], int num, unsigned char** data_bits, int* bytes, int* pos) {
+  legacy_compress(DCB_CT_BITWISE_NP, data, num, data_bits, bytes, pos, 0, NULL);
+}
+extern "C" float* myDecompress_bitwise_np(unsigned char* data_bits, int bytes, int num) {
+  return legacy_decompress(DCB_CT_BITWISE_NP, data_bits, bytes, num, 0, NULL);
+}
+extern "C" void myCompress_bitwise_op(float data[], int num, unsigned char** data_bits, int* bytes, int* pos) {
+  legacy_compress(DCB_CT_BITWISE_OP, data, num, data_bits, bytes, pos, 0, NULL);
+}
+extern "C" float* myDecompress_bitwise_op(unsigned char* data_bits, int bytes, int num) {
+  return legacy_decompress(DCB_CT_BITWISE_OP, data_bits, bytes, num, 0, NULL);
+}
+extern "C" void myCompress_bitwise_mask(float data[], int num, unsigned char** data_bits, int* bytes, int* pos, int type,
+                                        char mask[1 + 8 + 8]) {
+  legacy_compress(DCB_CT_BITWISE_MASK, data, num, data_bits, bytes, pos, type < 0 ? 0 : (type > 7 ? 7 : type), mask);
+}
+extern "C" float* myDecompress_bitwise_mask(unsigned char* data_bits, int bytes, int num, int type, char mask[1 + 8 + 8]) {
+  return legacy_decompress(DCB_CT_BITWISE_MASK, data_bits, bytes, num, type < 0 ? 0 : (type > 7 ? 7 : type), mask);
+}
+
+// ---- callers' front end ------------------------------------------------------------------------------------
+__global__ void dcb_subtract_kernel(const float* __restrict__ x, const float* __restrict__ mn, float* __restrict__ y, uint64_t n) {
+  const float m = *mn;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    y[i] = __fsub_rn(x[i], m);
+}
+
+struct DevBuf {
+  void* p = nullptr;
+  explicit DevBuf(size_t bytes) { if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) p = nullptr; }
+  ~DevBuf() { if (p) cudaFree(p); }
+};
+
+// toSmallDataset_float, dataCompression.c:3543-3562: min (first minimum wins), then data - min into a malloc'd array
+extern "C" float toSmallDataset_float(float data[], float** data_small, int num) {
+  *data_small = (float*)malloc(sizeof(float) * (size_t)(num > 0 ? num : 1));
+  if (!*data_small) { printf("ERROR: Out of memory\n"); exit(1); }
+  if (num <= 0) return 0.0f;
+  if (dcb_device_count() == 0) die("toSmallDataset_float (no CUDA device)", DCB_ENODEVICE);
+  const uint64_t n = (uint64_t)num;
+  DevBuf dx(n * 4), dy(n * 4), dm(16);
+  if (!dx.p || !dy.p || !dm.p) die("cudaMalloc", DCB_ECUDA);
+  float mn = 0.0f;
+  cudaMemcpy(dx.p, data, n * 4, cudaMemcpyHostToDevice);
+  int rc = dcb_chunk_stats((const float*)dx.p, n, 0, 0, (float*)dm.p, NULL, NULL, NULL);
+  if (rc != DCB_OK) die("dcb_chunk_stats", rc);
+  dcb_subtract_kernel<<<1184, 256>>>((const float*)dx.p, (const float*)dm.p, (float*)dy.p, n);
+  cudaMemcpy(*data_small, dy.p, n * 4, cudaMemcpyDeviceToHost);
+  if (cudaMemcpy(&mn, dm.p, 4, cudaMemcpyDeviceToHost) != cudaSuccess) die("toSmallDataset_float", DCB_ECUDA);
+  return mn;
+}
+
+// med_dataset_float, dataCompression.c:3593-3620: sequential float32 mean (exact: one thread walks the chain), max -> type
+extern "C" float med_dataset_float(float* data, int num, int* type) {
+  if (num <= 0) return 0.0f;
+  if (dcb_device_count() == 0) die("med_dataset_float (no CUDA device)", DCB_ENODEVICE);
+  const uint64_t n = (uint64_t)num;
+  DevBuf dx(n * 4), dm(48);
+  if (!dx.p || !dm.p) die("cudaMalloc", DCB_ECUDA);
+  cudaMemcpy(dx.p, data, n * 4, cudaMemcpyHostToDevice);
+  float* d_min = (float*)dm.p; float* d_med = d_min + 4; int32_t* d_ty = (int32_t*)(d_min + 8);
+  int rc = dcb_chunk_medium((const float*)dx.p, n, d_med, d_ty, NULL);
+  if (rc != DCB_OK) die("dcb_chunk_medium", rc);
+  float med = 0.0f; int32_t ty = 0;
+  cudaMemcpy(&med, d_med, 4, cudaMemcpyDeviceToHost);
+  if (cudaMemcpy(&ty, d_ty, 4, cudaMemcpyDeviceToHost) != cudaSuccess) die("med_dataset_float", DCB_ECUDA);
+  if (ty != 0) *type = ty;                       // max >= 2^127: the reference leaves *type untouched (:3605-3614)
+  return med;
+}
+
+// do_crc32, dataCompression.c:5524-5534 (zlib crc32 of the whole buffer)
+extern "C" uint32_t do_crc32(unsigned char* data_bits, int bytes) {
+  if (bytes <= 0) return 0u;
+  if (dcb_device_count() == 0) die("do_crc32 (no CUDA device)", DCB_ENODEVICE);
+  DevBuf ds((size_t)bytes + 16), dt(32);
+  if (!ds.p || !dt.p) die("cudaMalloc", DCB_ECUDA);
+  const uint64_t offs[2] = {0, (uint64_t)bytes};
+  cudaMemcpy(ds.p, data_bits, (size_t)bytes, cudaMemcpyHostToDevice);
+  cudaMemcpy(dt.p, offs, 16, cudaMemcpyHostToDevice);
+  uint32_t* d_crc = (uint32_t*)((char*)dt.p + 16);
+  int rc = dcb_crc32_chunks((const uint8_t*)ds.p, (const uint64_t*)dt.p, 1, d_crc, NULL);
+  if (rc != DCB_OK) die("dcb_crc32_chunks", rc);
+  uint32_t crc = 0;
+  if (cudaMemcpy(&crc, d_crc, 4, cudaMemcpyDeviceToHost) != cudaSuccess) die("do_crc32", DCB_ECUDA);
+  return crc;
+}
+
+// ---- bit-string helpers (pure formatting, dataCompression.c:5244-5276, :5512-5522) -----------------------------
+extern "C" void floattostr(float* a, char* str) {
+  uint32_t c;
+  memcpy(&c, a, 4);
+  for (int i = 0; i < 32; i++) str[i] = (char)('0' + ((c >> (31 - i)) & 1u));
+  str[32] = '\0';
+}
+extern "C" float strtofloat(char* str) {
+  uint32_t c = 0;
+  for (int i = 0; i < 32; i++) c = (c << 1) + (uint32_t)(str[i] - '0');
+  float f;
+  memcpy(&f, &c, 4);
+  return f;
+}
+extern "C" int to_absErrorBound_binary(double absErrBound) { return dcb_n_eb(absErrBound); }

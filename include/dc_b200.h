@@ -86,6 +86,10 @@ int dcb_crc32_chunks(const uint8_t* d_stream, const uint64_t* d_chunk_offsets, u
 int dcb_chunk_stats(const float* d_in, uint64_t n, uint64_t chunk_elems, int want_medium,
                     float* d_chunk_min, float* d_chunk_medium, int32_t* d_chunk_type, void* cuda_stream);
 
+/* med_dataset_float (:3593) of the whole array as it is (no min-subtract): exact sequential float32 mean, and the
+ * type from max (0 = "left at the caller's initial value") */
+int dcb_chunk_medium(const float* d_in, uint64_t n, float* d_medium, int32_t* d_type, void* cuda_stream);
+
 /* bit_flip (dataCompression.c:5858) test hook: flips bit (7 - bit_index%8) of byte bit_index/8 for each index */
 int dcb_flip_bits(uint8_t* d_stream, const uint64_t* d_bit_indices, uint64_t count, void* cuda_stream);
 
@@ -99,6 +103,10 @@ int dcb_decompress_host(int ct, const uint8_t* h_stream, const uint64_t* h_chunk
                         uint64_t chunk_elems, double abs_error_bound, uint32_t flags, int fixed_type,
                         uint32_t fixed_mask17, const float* h_chunk_min, const float* h_chunk_medium,
                         const int32_t* h_chunk_type, float* h_out);
+
+/* Bit length (before the final byte round-up) of the whole stream produced by this thread's most recent
+ * dcb_compress_host call: the legacy `pos` output is 8 - bits%8 (8 when aligned), dataCompression.c:5456-5489. */
+uint64_t dcb_last_stream_bits(void);
 
 #ifdef __cplusplus
 }
