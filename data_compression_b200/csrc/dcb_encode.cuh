@@ -139,17 +139,17 @@ __device__ __forceinline__ unsigned long long lookback_bits(const volatile unsig
 
 struct EncSmem {
   float X[2][DCB_NT * DCB_XPITCH];   // double-buffered input tiles, one 80-byte slot per thread
-  uint32_t W[DCB_TILE + 8];          // packed tile: W[0] = 0; stream word k of the tile lives at W[1 + k]
+  uint32_t W[2][DCB_TILE + 8];       // packed tiles (double buffered): W[b][0] = 0; stream word k of the tile lives at W[b][1 + k]
   float red_mn[2][DCB_NT / 32];      // partials of the block reductions, double buffered (see block_stats)
   float red_mx[2][DCB_NT / 32];
-  uint32_t red_ua[2][DCB_NT / 32];
+  float red_am[2][DCB_NT / 32];
   float red_s[2][DCB_NT / 32];
   uint32_t warp_tot[2][DCB_NT / 32];
   uint32_t xchg[DCB_NT / 32];        // tail word of every warp's last lane (completes the next warp's first word)
   float hx[2][DCB_NT / 32][4];       // last three RAW values of every warp (look-back of the next warp's lane 0)
   uint32_t tkt[2];                   // prefetched tickets
   unsigned long long P;              // absolute bit offset of the tile being copied out
-  uint32_t pend_tile, pend_bits, pend_c, pend_last;   // the tile packed in the previous iteration (finished one iteration later)
+  uint32_t pend_tile[2], pend_bits[2], pend_c[2], pend_last[2];   // tiles packed in the previous two iterations (each is finished two iterations later)
   float mn, med;
   int type;
   uint32_t fi;
@@ -177,21 +177,29 @@ __device__ __forceinline__ void issue_tile_load(const EncArgs& a, uint32_t tile,
   }
 }
 
-// One barrier: block-wide min, max and "largest |x| word" of the raw tile.  `par` alternates between
-// consecutive calls so that the partial arrays need no trailing barrier.
-__device__ __forceinline__ void block_stats(float& mn, float& mx, uint32_t& ua, EncSmem& sm, int par, int lane, int warp) {
+// max that PROPAGATES NaN (fmaxf drops it): one instruction (FMNMX.NAN), used to spot NaN/Inf/huge values
+__device__ __forceinline__ float fmax_nan(float a, float b) {
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+
+// One barrier: block-wide min, [max, CT=7 only] and NaN-propagating max of |x| of the raw tile.  `par` alternates
+// between consecutive calls so that the partial arrays need no trailing barrier.
+template <bool WANT_MAX>
+__device__ __forceinline__ void block_stats(float& mn, float& mx, float& am, EncSmem& sm, int par, int lane, int warp) {
   #pragma unroll
   for (int o = 16; o; o >>= 1) {
     mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    ua = max(ua, __shfl_xor_sync(0xffffffffu, ua, o));
+    if (WANT_MAX) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    am = fmax_nan(am, __shfl_xor_sync(0xffffffffu, am, o));
   }
-  if (lane == 0) { sm.red_mn[par][warp] = mn; sm.red_mx[par][warp] = mx; sm.red_ua[par][warp] = ua; }
+  if (lane == 0) { sm.red_mn[par][warp] = mn; if (WANT_MAX) sm.red_mx[par][warp] = mx; sm.red_am[par][warp] = am; }
   __syncthreads();
-  mn = sm.red_mn[par][0]; mx = sm.red_mx[par][0]; ua = sm.red_ua[par][0];
+  mn = sm.red_mn[par][0]; if (WANT_MAX) mx = sm.red_mx[par][0]; am = sm.red_am[par][0];
   #pragma unroll
   for (int w = 1; w < DCB_NT / 32; w++) {
-    mn = fminf(mn, sm.red_mn[par][w]); mx = fmaxf(mx, sm.red_mx[par][w]); ua = max(ua, sm.red_ua[par][w]);
+    mn = fminf(mn, sm.red_mn[par][w]); if (WANT_MAX) mx = fmaxf(mx, sm.red_mx[par][w]); am = fmax_nan(am, sm.red_am[par][w]);
   }
 }
 __device__ __forceinline__ float block_sum_any_order(float v, EncSmem& sm, int par, int lane, int warp) {
@@ -210,7 +218,7 @@ __device__ __forceinline__ float block_sum_any_order(float v, EncSmem& sm, int p
                                 ((e) == 10 ? ((((chi) << 1) & 6u) | ((clo) >> 31)) : (((clo) >> (61 - 3 * (e))) & 7u)))
 
 // copy-out: shift the packed tile to the output bit alignment, MSB-first byte order, coalesced 32-bit words
-__device__ __forceinline__ void copy_out_tile(const EncArgs& a, const EncSmem& sm, unsigned long long P,
+__device__ __forceinline__ void copy_out_tile(const EncArgs& a, const uint32_t* W, unsigned long long P,
                                               uint32_t tile_bits, bool last_in_chunk, int tid) {
   unsigned long long Eabs = P + tile_bits;
   if (last_in_chunk) Eabs = (Eabs + 7ull) & ~7ull;          // zero padding of the chunk's last byte (:5467)
@@ -221,7 +229,7 @@ __device__ __forceinline__ void copy_out_tile(const EncArgs& a, const EncSmem& s
   const bool atomic_out = (a.flags & DCB_ENC_ATOMIC_OUT) != 0;
   for (unsigned long long g = g0 + tid; g <= g1; g += DCB_NT) {
     const uint32_t k = (uint32_t)(g - g0);
-    uint32_t v = sh ? __funnelshift_r(sm.W[1 + k], sm.W[k], sh) : sm.W[1 + k];
+    uint32_t v = sh ? __funnelshift_r(W[1 + k], W[k], sh) : W[1 + k];
     const bool head = (g == g0) && sh, tail = (g == g1) && tb;
     if (!head && !tail) {
       out32[g] = __byte_perm(v, 0u, 0x0123);
@@ -327,19 +335,19 @@ __device__ __noinline__ void scanner_role(const EncArgs& a, ScanSmem& ss, int ti
 }
 
 // thread 0 of a worker: wait for the inclusive prefix of tile-1, publish the chunk offset of the pending tile
-__device__ __forceinline__ void resolve_pending(const EncArgs& a, EncSmem& sm, unsigned long long w0) {
+__device__ __forceinline__ void resolve_pending(const EncArgs& a, EncSmem& sm, int b, unsigned long long w0) {
   volatile unsigned long long* status = a.status;
-  const uint32_t tile = sm.pend_tile;
+  const uint32_t tile = sm.pend_tile[b];
   unsigned long long P = 0ull;
   if (tile > 0u) {
     while ((w0 >> ST_SHIFT) != ST_INCL) { __nanosleep(20); w0 = status[tile - 1u]; }
     P = w0 & ST_VAL_MASK;
   }
-  unsigned long long E = P + sm.pend_bits;
+  unsigned long long E = P + sm.pend_bits[b];
   if (tile == a.num_tiles - 1u && a.last_bits) *a.last_bits = E;
   sm.P = P;
   if (tile == 0u) a.offsets[0] = 0ull;
-  if (sm.pend_last) a.offsets[(uint64_t)sm.pend_c + 1ull] = (E + 7ull) >> 3;
+  if (sm.pend_last[b]) a.offsets[(uint64_t)sm.pend_c[b] + 1ull] = (E + 7ull) >> 3;
 }
 
 template <int CT>
@@ -355,7 +363,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
     const uint32_t role = (a.num_tiles > 1u && atomicCAS(a.scanner_claim, 0u, 1u) == 0u) ? 1u : 0u;
     sm.role = role;
     if (!role) { sm.tkt[0] = atomicAdd(a.ticket, 1u); sm.tkt[1] = atomicAdd(a.ticket, 1u); }
-    sm.W[0] = 0u;
+    sm.W[0][0] = 0u; sm.W[1][0] = 0u;
   }
   __syncthreads();
   if (sm.role) { scanner_role(a, *reinterpret_cast<ScanSmem*>(sm.X[0]), tid); return; }
@@ -367,12 +375,12 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
   const bool submin = (a.flags & 1u) != 0;            // DCB_F_SUBTRACT_MIN
   const bool fixed_mask = (a.flags & 2u) != 0;        // DCB_F_FIXED_MASK
   const bool stats_ready = (a.flags & DCB_ENC_STATS_READY) != 0;
-  const uint32_t abs_mask = submin ? 0x7FFFFFFFu : 0xFFFFFFFFu;   // without min-subtract a negative value makes the tile SLOW
 
   uint32_t fix_hw = 0; bool fix_need = false;         // lane 0 of warps > 0: first word of the pending tile still lacks the previous warp's tail
   int par = 0;
 
-  for (uint32_t it = 0;; it++) {
+  uint32_t it = 0;
+  for (;; it++) {
     const int buf = (int)(it & 1u);
     float* slot = &sm.X[buf][tid * DCB_XPITCH];
     // ---- issue everything with a long latency for LATER use -------------------------------------------
@@ -381,8 +389,9 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
     uint32_t tk = 0u;
     if (tid == 0) tk = atomicAdd(a.ticket, 1u);                         // ticket of the tile after next
     unsigned long long w0 = 0ull;                                       // inclusive prefix of the tile before the pending one
-    if (tid == 0 && it > 0u && sm.pend_tile > 0u) w0 = status[sm.pend_tile - 1u];
-    if (fix_need) sm.W[fix_hw] |= sm.xchg[warp - 1];                    // (ordered before the copy-out by the barriers below)
+    if (tid == 0 && it > 1u && sm.pend_tile[buf] > 0u) w0 = status[sm.pend_tile[buf] - 1u];   // tile packed two iterations ago
+    uint32_t* const W = sm.W[buf];                                      // staging buffer of the current tile (and of the one two iterations ago)
+    if (fix_need) sm.W[buf ^ 1][fix_hw] |= sm.xchg[warp - 1];           // previous tile (ordered before its copy-out by the barriers in between)
     fix_need = false;
 
     // ---- chunk geometry of the current tile ---------------------------------------------------------------
@@ -415,25 +424,38 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
 
     // ---- 2. one block reduction: min (toSmallDataset_float :3543-3562), max (type), largest |x| word (FAST test) --
     float lmn = __uint_as_float(0x7f800000u), lmx = __uint_as_float(0xff800000u);
-    uint32_t ua = 0u;
+    float am = 0.0f;                                   // NaN-propagating max |x|: NaN, Inf and |x| >= 2^127 all end up >= 2^127 or NaN
+    bool negative = false;                             // without min-subtract a negative value (sign bit set, -0.0f included) makes the tile SLOW
     if (full) {
       #pragma unroll
-      for (int e = 0; e < DCB_E; e++) { lmn = fminf(lmn, x[e]); lmx = fmaxf(lmx, x[e]); ua = max(ua, f2u(x[e]) & abs_mask); }
+      for (int e = 0; e < DCB_E; e++) {
+        lmn = fminf(lmn, x[e]);
+        if (CT == CT_MASK) lmx = fmaxf(lmx, x[e]);
+        am = fmax_nan(am, fabsf(x[e]));
+      }
     } else {
       #pragma unroll
       for (int e = 0; e < DCB_E; e++) {
-        if (e < vcnt) { lmn = fminf(lmn, x[e]); lmx = fmaxf(lmx, x[e]); }         // NaN never wins a '<' (:3550)
-        ua = max(ua, f2u(x[e]) & abs_mask);                                        // padding is 0.0f
+        if (e < vcnt) { lmn = fminf(lmn, x[e]); if (CT == CT_MASK) lmx = fmaxf(lmx, x[e]); }   // NaN never wins a '<' (:3550)
+        am = fmax_nan(am, fabsf(x[e]));                                                          // padding is 0.0f
       }
     }
-    if (tid == 0) ua = max(ua, max(f2u(hr1) & abs_mask, max(f2u(hr2) & abs_mask, f2u(hr3) & abs_mask)));
+    if (!submin) {
+      uint32_t sg = 0u;
+      #pragma unroll
+      for (int e = 0; e < DCB_E; e++) sg |= f2u(x[e]);
+      if (tid == 0) sg |= f2u(hr1) | f2u(hr2) | f2u(hr3);
+      negative = (sg >> 31) != 0u;
+      if (negative) am = __uint_as_float(0x7fc00000u);                              // fold into the same reduction
+    }
+    if (tid == 0) am = fmax_nan(am, fmax_nan(fabsf(hr1), fmax_nan(fabsf(hr2), fabsf(hr3))));
     if (lane == 31) { sm.hx[par][warp][0] = x[DCB_E - 1]; sm.hx[par][warp][1] = x[DCB_E - 2]; sm.hx[par][warp][2] = x[DCB_E - 3]; }
-    block_stats(lmn, lmx, ua, sm, par, lane, warp);
+    block_stats<CT == CT_MASK>(lmn, lmx, am, sm, par, lane, warp);
     float mn = 0.0f;
     if (submin) mn = stats_ready ? a.cmin[c] : lmn;
     // FAST tile: every |x| (and |min|) below 2^127, so x - min is finite and >= 0; no NaN/Inf; no negative value
     // without min-subtract.  Negative values include the -1.0f "empty history slot" sentinel.
-    bool slow = (ua >= 0x7F000000u) || ((f2u(mn) & 0x7FFFFFFFu) >= 0x7F000000u);
+    bool slow = !(am < 1.7014118e38f) || !(fabsf(mn) < 1.7014118e38f);     // 2^127; NaN fails both
     if (submin && !stats_ready) {
       if (mn == 0.0f) {
         // +0 / -0 compare equal: the reference keeps the FIRST minimal element; recover its sign
@@ -661,11 +683,11 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
       status[tile] = (ST_AGG << ST_SHIFT) | ((last_in_chunk && !single) ? ST_END_BIT : 0ull) | v;
     }
 
-    // ---- 5. finish the PREVIOUS tile: its start offset (status word loaded at the top), copy-out of the staging buffer ----
-    if (it > 0u) {
-      if (tid == 0) resolve_pending(a, sm, w0);
+    // ---- 5. finish the tile packed TWO iterations ago: its start offset (status word loaded at the top), copy-out of its staging buffer ----
+    if (it > 1u) {
+      if (tid == 0) resolve_pending(a, sm, buf, w0);
       __syncthreads();
-      copy_out_tile(a, sm, sm.P, sm.pend_bits, sm.pend_last != 0u, tid);
+      copy_out_tile(a, W, sm.P, sm.pend_bits[buf], sm.pend_last[buf] != 0u, tid);
       __syncthreads();
     }
 
@@ -680,8 +702,8 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
         const uint32_t w0_ = chi >> f0;
         const uint32_t w1_ = __funnelshift_r(clo, chi, f0);
         const uint32_t w2_ = __funnelshift_r(0u, clo, f0);
-        sm.W[hw] = w0_;
-        if (f0 >= 16u) { sm.W[hw + 1] = w1_; hi = w2_; widx = hw + 2; }
+        W[hw] = w0_;
+        if (f0 >= 16u) { W[hw + 1] = w1_; hi = w2_; widx = hw + 2; }
         else { hi = w1_; widx = hw + 1; }
       } else {
         uint32_t fill = f0;
@@ -692,7 +714,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
           const uint32_t lo = __funnelshift_r(0u, cl, fill);
           fill += (uint32_t)len[e];
           const bool fl = fill >= 32u;
-          if (fl) sm.W[widx] = hi;
+          if (fl) W[widx] = hi;
           widx += fl ? 1u : 0u;
           hi = fl ? lo : hi;
           fill &= 31u;
@@ -700,17 +722,17 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
       }
       // the word straddling two threads is stored by the later one; it ORs in the earlier thread's tail
       const uint32_t prevT = __shfl_up_sync(0xffffffffu, hi, 1);
-      if (lane > 0 && total > 0u && f0) sm.W[hw] |= prevT;
+      if (lane > 0 && total > 0u && f0) W[hw] |= prevT;
       if (lane == 31) sm.xchg[warp] = hi;
       if (total > 0u && s + total == tile_bits) {          // last thread that has bits: flush its tail, zero what follows
-        if ((s + total) & 31u) sm.W[widx++] = hi;
-        sm.W[widx] = 0u; sm.W[widx + 1] = 0u;
+        if ((s + total) & 31u) W[widx++] = hi;
+        W[widx] = 0u; W[widx + 1] = 0u;
       }
       fix_need = (lane == 0 && warp > 0 && total > 0u && f0 != 0u);   // completed at the top of the next iteration
       fix_hw = hw;
     } else {
       // ragged tile (fewer than 11 valid elements in some thread): zero the buffer and OR every word in
-      for (int i = tid + 1; i < DCB_TILE + 8; i += DCB_NT) sm.W[i] = 0u;
+      for (int i = tid + 1; i < DCB_TILE + 8; i += DCB_NT) W[i] = 0u;
       __syncthreads();
       uint32_t fill = f0, widx = hw;
       if (all3) {                                          // (cannot happen: all3 implies 48 bits; kept for safety)
@@ -725,15 +747,15 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
           hi |= cl >> fill;
           const uint32_t lo = __funnelshift_r(0u, cl, fill);
           fill += L;
-          if (fill >= 32u) { atomicOr(&sm.W[widx++], hi); hi = lo; fill -= 32u; }
+          if (fill >= 32u) { atomicOr(&W[widx++], hi); hi = lo; fill -= 32u; }
         }
       }
-      if (fill && total > 0u) atomicOr(&sm.W[widx], hi);
+      if (fill && total > 0u) atomicOr(&W[widx], hi);
     }
 
     // ---- 7. rotate the pipeline --------------------------------------------------------------------------
     if (tid == 0) {
-      sm.pend_tile = tile; sm.pend_bits = tile_bits; sm.pend_c = c; sm.pend_last = last_in_chunk ? 1u : 0u;
+      sm.pend_tile[buf] = tile; sm.pend_bits[buf] = tile_bits; sm.pend_c[buf] = c; sm.pend_last[buf] = last_in_chunk ? 1u : 0u;
       sm.tkt[buf] = tk;                                  // slot of the ticket just consumed
     }
     par ^= 1;
@@ -743,9 +765,18 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
     if (cur >= a.num_tiles) break;
   }
 
-  // ---- epilogue: finish the last tile of this block ---------------------------------------------------------
-  if (fix_need) sm.W[fix_hw] |= sm.xchg[warp - 1];
-  if (tid == 0) resolve_pending(a, sm, 0ull);
-  __syncthreads();
-  copy_out_tile(a, sm, sm.P, sm.pend_bits, sm.pend_last != 0u, tid);
+  // ---- epilogue: finish the last two tiles of this block (older first) --------------------------------------
+  // here `it` is the index of the last iteration executed; its tile sits in W[it & 1], the one before in W[(it & 1) ^ 1]
+  {
+    const int lastb = (int)(it & 1u);
+    if (fix_need) sm.W[lastb][fix_hw] |= sm.xchg[warp - 1];
+    __syncthreads();
+    for (int k = (it > 0u ? 0 : 1); k < 2; k++) {
+      const int b = (k == 0) ? (lastb ^ 1) : lastb;
+      if (tid == 0) resolve_pending(a, sm, b, 0ull);
+      __syncthreads();
+      copy_out_tile(a, sm.W[b], sm.P, sm.pend_bits[b], sm.pend_last[b] != 0u, tid);
+      __syncthreads();
+    }
+  }
 }
