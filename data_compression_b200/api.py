@@ -18,7 +18,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG, "libdcb200.so")
 
 CT_BITWISE, CT_BITWISE_NP, CT_BITWISE_MASK, CT_BITWISE_CRC, CT_MASK_CRC, CT_BITWISE_OP = 5, 6, 7, 8, 9, 11
-F_SUBTRACT_MIN, F_FIXED_MASK, F_CRC = 1, 2, 4
+F_SUBTRACT_MIN, F_FIXED_MASK, F_CRC, F_EXACT_MEDIUM = 1, 2, 4, 8
 TILE_ELEMS = 4096
 DEFAULT_CHUNK = 4096
 
@@ -155,14 +155,14 @@ class Workspace:
 
 
 def compress(x, ct=CT_BITWISE, abs_error_bound=1e-6, chunk_elems=DEFAULT_CHUNK, subtract_min=True,
-             fixed_type=None, fixed_mask17=None, crc=False, workspace=None):
+             fixed_type=None, fixed_mask17=None, crc=False, workspace=None, exact_medium=False):
     """x: contiguous float32 CUDA tensor.  One chunk == one reference call myCompress_bitwise*(..., (NULL,0,8))."""
     import torch
     if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()):
         raise DcbError("compress() needs a contiguous float32 CUDA tensor (there is no CPU path)")
     n = x.numel()
     ws = workspace or Workspace(n, chunk_elems, x.device)
-    flags = (F_SUBTRACT_MIN if subtract_min else 0) | (F_CRC if crc else 0)
+    flags = (F_SUBTRACT_MIN if subtract_min else 0) | (F_CRC if crc else 0) | (F_EXACT_MEDIUM if exact_medium else 0)
     ft, fm = 0, 0
     if fixed_type is not None:
         flags |= F_FIXED_MASK

@@ -156,7 +156,7 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
   a.chunk = single ? n : chunk;
   a.num_tiles = (uint32_t)num_tiles(n);
   a.tiles_per_chunk = single ? 0u : (uint32_t)(chunk / DCB_TILE);
-  a.flags = flags & 7u;
+  a.flags = flags & 15u;
   a.fixed_type = fixed_type; a.fixed_mask17 = fixed_mask17;
   a.out = d_stream; a.offsets = d_offsets; a.cmin = d_cmin; a.cmed = d_cmed; a.ctype = d_ctype;
   a.ticket = (unsigned int*)d_ws;

@@ -148,6 +148,7 @@ struct EncSmem {
   uint32_t xchg[DCB_NT / 32];        // tail word of every warp's last lane (completes the next warp's first word)
   float hx[2][DCB_NT / 32][4];       // last three RAW values of every warp (look-back of the next warp's lane 0)
   uint32_t tkt[2];                   // prefetched tickets
+  uint32_t walkmask[DCB_NT / 32];    // exact-sum fallback: threads where the serial walk has to stop
   unsigned long long P;              // absolute bit offset of the tile being copied out
   uint32_t pend_tile[2], pend_bits[2], pend_c[2], pend_last[2];   // tiles packed in the previous two iterations (each is finished two iterations later)
   float mn, med;
@@ -518,10 +519,12 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
         // u = 2^-24).  If both ends of the bracket give the same 17 bits the mask is decided without the
         // 4096-step dependent chain; otherwise (and for SLOW tiles) one thread runs the chain exactly.
         bool decided = false;
+        float ps = 0.0f;
         if (!slow) {
-          float ps = 0.0f;
           #pragma unroll
           for (int e = 0; e < DCB_E; e++) ps = __fadd_rn(ps, x[e]);
+        }
+        if (!slow && !(a.flags & 8u)) {                      // DCB_F_EXACT_MEDIUM skips the shortcut
           const float S = block_sum_any_order(ps, sm, par, lane, warp);
           const float rel = (float)(cnt + 64) * (1.02f / 16777216.0f);
           const float lo = __fmul_rd(S, __fsub_rd(1.0f, rel)), hi = __fmul_ru(S, __fadd_ru(1.0f, rel));
@@ -535,6 +538,13 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
           }
         }
         if (!decided) {                                    // block-uniform
+          // Exact sequential sum.  While the running sum S stays inside one binade [2^e, 2^(e+1)) it lives on the grid
+          // q = 2^(e-23), and S -> fl(S + y) commutes with shifts of S by 2q (round-to-nearest-even only looks at the
+          // position relative to the grid and at the parity of S/q).  So a thread whose 16 values provably neither
+          // start nor end outside one binade is a 2-state transducer: S_out = S_in + d[parity(S_in)], and d[0], d[1]
+          // come from two 16-step chains started at 2^e and 2^e + q -- all threads in parallel.  Thread 0 then walks
+          // the 256 transducers (one exact add each) and chains the few threads that straddle a binade element by
+          // element: ~3k dependent cycles instead of 16k.  SLOW tiles (negative / NaN / Inf) keep the plain chain.
           #pragma unroll
           for (int e = 0; e < DCB_E; e++) slot[e] = x[e];  // the consumed input slot doubles as the staging for thread 0
           float ymx = __uint_as_float(0xff800000u);
@@ -542,26 +552,88 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
           for (int e = 0; e < DCB_E; e++) if (e < vcnt) ymx = fmaxf(ymx, x[e]);
           #pragma unroll
           for (int o = 16; o; o >>= 1) ymx = fmaxf(ymx, __shfl_xor_sync(0xffffffffu, ymx, o));
+          float inc = ps;
+          #pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const float t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc = __fadd_rn(inc, t);
+          }
+          __syncthreads();                                 // every read of red_s / red_mx of this iteration is done
+          if (lane == 0) sm.red_mx[par][warp] = ymx;
+          if (lane == 31) sm.red_s[par][warp] = inc;
           __syncthreads();
-          if (lane == 0) sm.red_s[par][warp] = ymx;
-          __syncthreads();
-          if (tid == 0) {
-            float mx = sm.red_s[par][0];
-            #pragma unroll
-            for (int w = 1; w < DCB_NT / 32; w++) mx = fmaxf(mx, sm.red_s[par][w]);
-            float total = 0.0f;
-            const float* Y = sm.X[buf];
-            int i = 0;
-            for (; i + DCB_E <= cnt; i += DCB_E) {
-              const float* yp = Y + (i / DCB_E) * DCB_XPITCH;
+          float d0 = -1.0f, d1 = -1.0f;                    // < 0: chain this thread's values from the exact running sum
+          float lo_keep = 0.0f;
+          if (!slow) {
+            float wb = 0.0f;
+            for (int w = 0; w < warp; w++) wb = __fadd_rn(wb, sm.red_s[par][w]);
+            const float pex = __fadd_rn(wb, __fsub_rn(inc, ps));           // estimate of the running sum before this thread
+            // |reference running sum - pex| <= (16 tid [its roundings] + 30 [ours]) u * sum; 96 and 1.02 leave slack
+            const float relt = (float)(16 * tid + 96) * (1.02f / 16777216.0f);
+            const float lo = __fmul_rd(pex, __fsub_rd(1.0f, relt));
+            float hi = __fmul_ru(__fadd_ru(pex, ps), __fadd_ru(1.0f, relt));
+            hi = __fmul_ru(hi, 1.00001f);                                   // the 16 round-ups inside the thread and the +q start
+            const uint32_t elo = f2u(lo) >> 23, ehi = f2u(hi) >> 23;
+            lo_keep = lo;
+            if (elo == ehi && elo > 0u && elo < 255u) {
+              const float r0 = u2f(elo << 23), r1 = u2f((elo << 23) | 1u);
+              float c0 = r0, c1 = r1;
               #pragma unroll
-              for (int q = 0; q < 4; q++) {
-                const float4 v = *reinterpret_cast<const float4*>(yp + 4 * q);
-                total = __fadd_rn(total, v.x); total = __fadd_rn(total, v.y);
-                total = __fadd_rn(total, v.z); total = __fadd_rn(total, v.w);
+              for (int e = 0; e < DCB_E; e++) { c0 = __fadd_rn(c0, x[e]); c1 = __fadd_rn(c1, x[e]); }
+              d0 = __fsub_rn(c0, r0); d1 = __fsub_rn(c1, r1);               // exact: both ends lie on the grid of one binade
+            }
+          }
+          // Runs of consecutive transducer threads in the same binade compose (associatively) into one transducer:
+          // segmented warp scan.  (E then O)_p = E_p + O_{p ^ parity(E_p / q)}; every sum is exact (< 2^e, on the grid).
+          {
+            const bool certain = d0 >= 0.0f;
+            const unsigned cm = __ballot_sync(0xffffffffu, certain);
+            const uint32_t ebits = certain ? (f2u(lo_keep) >> 23) : 0u;
+            const uint32_t eprev = __shfl_up_sync(0xffffffffu, ebits, 1);
+            const bool head = certain && (lane == 0 || !((cm >> (lane - 1)) & 1u) || eprev != ebits);
+            const unsigned hm = __ballot_sync(0xffffffffu, head);
+            const int rs = 31 - __clz((int)(hm & (0xFFFFFFFFu >> (31 - lane))));    // first lane of this lane's run
+            const float r0 = u2f(ebits << 23);
+            #pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+              const float e0 = __shfl_up_sync(0xffffffffu, d0, o), e1 = __shfl_up_sync(0xffffffffu, d1, o);
+              if (certain && lane - o >= rs) {
+                const bool q0 = (f2u(__fadd_rn(r0, e0)) & 1u) != 0u, q1 = (f2u(__fadd_rn(r0, e1)) & 1u) != 0u;
+                const float n0 = __fadd_rn(e0, q0 ? d1 : d0), n1 = __fadd_rn(e1, q1 ? d0 : d1);
+                d0 = n0; d1 = n1;
               }
             }
-            for (; i < cnt; i++) total = __fadd_rn(total, Y[(i / DCB_E) * DCB_XPITCH + (i % DCB_E)]);
+            const bool tail = certain && (lane == 31 || ((hm >> (lane + 1)) & 1u) || !((cm >> (lane + 1)) & 1u));
+            const unsigned wp = __ballot_sync(0xffffffffu, !certain || tail);       // where thread 0 has to stop
+            if (lane == 0) sm.walkmask[warp] = wp;
+          }
+          slot[16] = d0; slot[17] = d1;
+          __syncthreads();
+          if (tid == 0) {
+            float mx = sm.red_mx[par][0];
+            #pragma unroll
+            for (int w = 1; w < DCB_NT / 32; w++) mx = fmaxf(mx, sm.red_mx[par][w]);
+            float total = 0.0f;
+            const float* Y = sm.X[buf];
+            for (int w = 0; w < DCB_NT / 32; w++) {
+              unsigned m = sm.walkmask[w];
+              while (m) {
+                const int t = w * 32 + (__ffs((int)m) - 1);
+                m &= m - 1u;
+                const float* yp = Y + t * DCB_XPITCH;
+                const float2 d = *reinterpret_cast<const float2*>(yp + 16);
+                if (d.x >= 0.0f) {
+                  total = __fadd_rn(total, (f2u(total) & 1u) ? d.y : d.x);    // exact
+                } else {
+                  #pragma unroll
+                  for (int q = 0; q < 4; q++) {
+                    const float4 v = *reinterpret_cast<const float4*>(yp + 4 * q);
+                    total = __fadd_rn(total, v.x); total = __fadd_rn(total, v.y);
+                    total = __fadd_rn(total, v.z); total = __fadd_rn(total, v.w);
+                  }
+                }
+              }
+            }
             const float med = __fdiv_rn(total, (float)cnt);
             const int ty = (Y[0] != Y[0]) ? 0 : type_from_max(mx);   // max starts at data[0]: NaN there defeats every '<'
             sm.med = med; sm.type = ty;

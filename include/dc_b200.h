@@ -36,6 +36,7 @@ extern "C" {
 #define DCB_F_SUBTRACT_MIN 1u   /* fuse toSmallDataset_float (:3543) per chunk on compress; add min back on decompress (impl/pingpong.c:562) */
 #define DCB_F_FIXED_MASK   2u   /* CT=7/9: use (fixed_type, fixed_mask17) for every chunk instead of med_dataset_float (:3593) per chunk */
 #define DCB_F_CRC          4u   /* also write do_crc32 (:5524) of every chunk's stream (implied by CT=8/9) */
+#define DCB_F_EXACT_MEDIUM 8u   /* CT=7/9: d_chunk_medium holds med_dataset_float's exact float (default: only its 17 mask bits are defined) */
 
 #define DCB_OK            0
 #define DCB_EINVAL       -1     /* bad argument (ct, error bound, alignment, chunk size) */

@@ -140,6 +140,32 @@ def test_encoder_only_inputs(ct, dev):
     assert np.isnan(comp.chunk_min[0].item()) and not np.isnan(comp.chunk_min[1].item())
 
 
+def test_exact_medium_transducer_sum(dev):
+    """DCB_F_EXACT_MEDIUM: med_dataset_float's sequential float32 mean, bit for bit, from the parallel
+    binade-transducer sum (dcb_encode.cuh) -- on data that crosses many binades, has ties, zeros and tiny values."""
+    rng = np.random.default_rng(31)
+    n = 4096 * 24
+    fields = {
+        "noisy": make_field("noisy", n), "smooth": make_field("smooth", n), "constant": make_field("constant", n),
+        "lognormal": np.exp(rng.normal(0, 4, n)).astype(np.float32),
+        "small_ints": rng.integers(0, 5, n).astype(np.float32),                 # exact ties at every binade
+        "halves": (rng.integers(0, 64, n) * 0.5).astype(np.float32),
+        "sparse": np.where(rng.random(n) < 0.05, rng.random(n) * 1e6, 0).astype(np.float32),
+        "growing": (np.arange(n) % 4096).astype(np.float32) ** 2,
+        "tiny_then_big": np.where((np.arange(n) % 4096) < 2048, 1e-30, 3.0).astype(np.float32),
+    }
+    for name, x in fields.items():
+        for sub in (True, False):
+            xd = torch.from_numpy(x).to(dev)
+            comp = api.compress(xd, ct=7, abs_error_bound=0.01, chunk_elems=4096, subtract_min=sub, exact_medium=True)
+            torch.cuda.synchronize()
+            enc = ol.o_compress_chunked(7, x, 4096, 0.01, subtract_min=sub)
+            K = len(enc["offsets"]) - 1
+            assert np.array_equal(comp.chunk_medium[:K].cpu().numpy().view(np.uint32), enc["chunk_medium"].view(np.uint32)), (name, sub)
+            assert np.array_equal(comp.chunk_type[:K].cpu().numpy(), enc["chunk_type"]), (name, sub)
+            assert np.array_equal(comp.stream[:comp.total_bytes()].cpu().numpy(), enc["stream"]), (name, sub)
+
+
 def test_golden_fixtures(dev, golden_dir):
     """Committed outputs of the UNMODIFIED reference (tests/golden/make_golden.py)."""
     d = np.load(os.path.join(golden_dir, "datasets.npz"))
