@@ -302,6 +302,13 @@ def run_ours(a):
         return
 
     peak, peak_src = measured_peak()
+    traffic = None                                  # dram bytes per launch of the dominant kernel, from the committed ncu capture
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        key = "ct%d/%s/2^%d/eb%g/chunk%d" % (a.ct, a.field, a.log2n, a.eb, a.chunk)
+        traffic = tj.get(key)
+    except Exception:
+        pass
     B = float(total_bytes)
     alg_c, alg_d = 4.0 * n + B, B + 4.0 * n
     dom = "dcb_encode_kernel" if tc_ms >= td_ms else "dcb_decode_kernel"
@@ -320,7 +327,8 @@ def run_ours(a):
                    "roundtrip_frac_of_hbm": ((alg_c + alg_d) / ((tc_ms + td_ms) * 1e-3) / 1e9) / peak,
                    "decode_status_ok": ok},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
-                     "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": ach / peak, "traffic": (traffic or {}).get(dom), "traffic_source": (traffic or {}).get("source"),
+                     "peak_source": peak_src,
                      "compress": {"achieved": alg_c / tc_ms / 1e6, "frac": alg_c / tc_ms / 1e6 / peak},
                      "decompress": {"achieved": alg_d / td_ms / 1e6, "frac": alg_d / td_ms / 1e6 / peak}},
         "clocks": clocks, "gpu_launches": launches_per_step * a.steps,

@@ -1,0 +1,147 @@
+"""Moving compressed chunks between GPUs: chunk-range sharding and the send/recv frames that replace the
+MPI messages of the reference's drivers.
+
+* shard_range(): SURVEY.md 8(e) -- chunks are independent and byte aligned, so rank g of G takes the contiguous chunk
+  range [g*K/G, (g+1)*K/G) and compresses it with no data-path collective.
+* send_compressed() / recv_compressed(): the pingpong hop (impl/pingpong.c:250 MPI_Send / :353 MPI_Recv of
+  data_bits) and the Himeno halo hop (impl/himenoBMTxps.c:667-693: the byte count first, then min + stream).  NCCL
+  needs matching counts on both ends, so a hop is two messages exactly like the reference's: a fixed-size header
+  with the chunk table (size known from n and chunk_elems), then the stream bytes the header announced.
+* pingpong_hop_crc(): the CT=8/9 protocol of impl/pingpong.c:260-289 (sender) and :363-447 (receiver): stream,
+  CRC, one-byte ack 'y'/'n', resend on 'n'.
+
+torch.distributed is the plumbing (backend "nccl" over NVLink on the GPU box, "gloo" in the CPU tests); the payload is
+whatever device the tensors live on.  Nothing here encodes or decodes.
+"""
+from dataclasses import dataclass
+from typing import Callable, Optional
+
+import numpy as np
+
+HEADER_WORDS = 8          # int64 words: magic, ct, n, chunk_elems, abs_error_bound (bits), flags|fixed_type<<8, fixed_mask17, total_bytes
+MAGIC = 0x44434232303042  # "DCB200B"
+
+
+def shard_range(n, chunk_elems, rank, world):
+    """-> (first_element, end_element) of rank's contiguous chunk range; ragged last chunk goes to the last rank."""
+    if chunk_elems <= 0 or chunk_elems >= n:
+        return (0, n) if rank == 0 else (n, n)          # a single chunk does not shard
+    K = (n + chunk_elems - 1) // chunk_elems
+    c0, c1 = rank * K // world, (rank + 1) * K // world
+    return min(n, c0 * chunk_elems), min(n, c1 * chunk_elems)
+
+
+def num_chunks(n, chunk_elems):
+    if n == 0:
+        return 0
+    return 1 if (chunk_elems <= 0 or chunk_elems >= n) else (n + chunk_elems - 1) // chunk_elems
+
+
+def table_words(K):
+    """int64 words of the header message: fixed header + offsets[K+1] + (min, medium, type, crc)[K] packed 2 x 32 bit."""
+    return HEADER_WORDS + (K + 1) + 2 * K
+
+
+@dataclass
+class Frame:
+    """One compressed array on the wire: header+table message and stream message (both torch tensors)."""
+    table: "object"      # int64 [table_words(K)]
+    stream: "object"     # uint8 [total_bytes]
+
+
+def pack_frame(comp):
+    """comp: api.Compressed (or anything with the same fields) -> Frame on comp's device."""
+    import torch
+    K = comp.chunk_offsets.numel() - 1
+    dev = comp.stream.device
+    t = torch.zeros(table_words(K), dtype=torch.int64, device=dev)
+    eb_bits = int(np.array([comp.abs_error_bound], dtype=np.float64).view(np.int64)[0])
+    total = int(comp.chunk_offsets[-1].item()) if K else 0
+    hdr = [MAGIC, comp.ct, comp.n, comp.chunk_elems, eb_bits, (comp.flags & 0xFF) | (comp.fixed_type << 8),
+           comp.fixed_mask17, total]
+    t[:HEADER_WORDS] = torch.tensor(hdr, dtype=torch.int64, device=dev)
+    t[HEADER_WORDS:HEADER_WORDS + K + 1] = comp.chunk_offsets
+    if K:
+        side = torch.zeros(4 * K, dtype=torch.int32, device=dev)
+        for i, f in enumerate((comp.chunk_min, comp.chunk_medium, comp.chunk_type, comp.chunk_crc)):
+            if f is not None:
+                side[i * K:(i + 1) * K] = f[:K].view(torch.int32)
+        t[HEADER_WORDS + K + 1:] = side.view(torch.int64)
+    return Frame(t, comp.stream[:total])
+
+
+def unpack_frame(frame, compressed_cls):
+    """Inverse of pack_frame -> compressed_cls(ct, n, chunk_elems, eb, flags, fixed_type, fixed_mask17, stream, offsets,
+    chunk_min, chunk_medium, chunk_type, chunk_crc)."""
+    import torch
+    t = frame.table
+    hdr = [int(v) for v in t[:HEADER_WORDS].tolist()]
+    if hdr[0] != MAGIC:
+        raise ValueError("not a dcb200 frame")
+    ct, n, chunk = hdr[1], hdr[2], hdr[3]
+    eb = float(np.array([hdr[4]], dtype=np.int64).view(np.float64)[0])
+    flags, ftype, fmask = hdr[5] & 0xFF, hdr[5] >> 8, hdr[6]
+    K = num_chunks(n, chunk)
+    offs = t[HEADER_WORDS:HEADER_WORDS + K + 1].clone()
+    side = t[HEADER_WORDS + K + 1:].contiguous().view(torch.int32) if K else torch.zeros(0, dtype=torch.int32)
+    cmin = side[0:K].view(torch.float32) if K else None
+    cmed = side[K:2 * K].view(torch.float32) if K else None
+    ctype = side[2 * K:3 * K] if K else None
+    ccrc = side[3 * K:4 * K] if K else None
+    return compressed_cls(ct, n, chunk, eb, flags, ftype, fmask, frame.stream, offs, cmin, cmed, ctype, ccrc)
+
+
+def send_compressed(comp, dst, group=None):
+    """Two messages, as impl/himenoBMTxps.c:667-693 sends `bytes` first: table (fixed size), then the stream."""
+    import torch.distributed as dist
+    f = pack_frame(comp)
+    dist.send(f.table, dst, group=group)
+    if f.stream.numel():
+        dist.send(f.stream.contiguous(), dst, group=group)
+    return f
+
+
+def recv_compressed(n, chunk_elems, src, device, compressed_cls, group=None, stream_buffer=None):
+    """Posts the fixed-size table receive, reads total_bytes from it, then receives exactly that many stream bytes."""
+    import torch
+    import torch.distributed as dist
+    K = num_chunks(n, chunk_elems)
+    t = torch.empty(table_words(K), dtype=torch.int64, device=device)
+    dist.recv(t, src, group=group)
+    total = int(t[HEADER_WORDS - 1].item())
+    cap = 4 * n + 16                                            # worst case of the stream (every code <= 32 bits)
+    if total > cap:
+        raise ValueError("frame announces %d bytes for %d values" % (total, n))
+    buf = stream_buffer if stream_buffer is not None else torch.zeros(((cap + 15) // 16) * 16, dtype=torch.uint8, device=device)
+    if total:
+        dist.recv(buf[:total], src, group=group)
+    return unpack_frame(Frame(t, buf), compressed_cls)
+
+
+def pingpong_hop_crc(comp, peer, is_sender, n, chunk_elems, device, compressed_cls,
+                     crc_fn: Callable, corrupt_fn: Optional[Callable] = None, max_resend=8, group=None):
+    """CT=8/9 hop.  Sender (impl/pingpong.c:260-289): send stream + per-chunk CRC (they travel in the table), wait for
+    the one-byte ack, resend on 'n'.  Receiver (:363-447): [test hook: corrupt the received stream, the reference's
+    bit_flip], recompute the CRC of what arrived, compare, ack.  Returns (Compressed the receiver holds | None, resends)."""
+    import torch
+    import torch.distributed as dist
+    resend = 0
+    ack = torch.zeros(1, dtype=torch.uint8, device=device)
+    while True:
+        if is_sender:
+            send_compressed(comp, peer, group=group)
+            dist.recv(ack, peer, group=group)
+            if ack.item() == ord("y") or resend >= max_resend:
+                return None, resend
+            resend += 1
+        else:
+            got = recv_compressed(n, chunk_elems, peer, device, compressed_cls, group=group)
+            if corrupt_fn is not None:
+                corrupt_fn(got, resend)
+            K = got.chunk_offsets.numel() - 1
+            ok = bool((crc_fn(got.stream, got.chunk_offsets)[:K] == got.chunk_crc[:K]).all().item())
+            ack[0] = ord("y") if ok else ord("n")
+            dist.send(ack, peer, group=group)
+            if ok or resend >= max_resend:
+                return got, resend
+            resend += 1

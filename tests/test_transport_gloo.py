@@ -1,0 +1,146 @@
+"""world_size-2 `gloo` tests (CPU) of the N>1 host logic: chunk-range sharding and the send/recv frames of
+data_compression_b200/transport.py.  The codec work in these tests is done by the CPU oracle (test infrastructure);
+on the GPU box the same functions carry api.Compressed objects produced by the CUDA kernels."""
+import os
+import socket
+from dataclasses import dataclass
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from data_compression_b200 import transport as tr
+from data_compression_b200.fields import make_field
+
+torch = pytest.importorskip("torch")
+
+
+@dataclass
+class HostCompressed:                      # same field order as api.Compressed
+    ct: int
+    n: int
+    chunk_elems: int
+    abs_error_bound: float
+    flags: int
+    fixed_type: int
+    fixed_mask17: int
+    stream: object
+    chunk_offsets: object
+    chunk_min: object
+    chunk_medium: object
+    chunk_type: object
+    chunk_crc: object
+
+
+def oracle_compressed(x, ct, chunk, eb):
+    base = 5 if ct in (5, 8) else (7 if ct in (7, 9) else ct)
+    enc = ol.o_compress_chunked(base, x, chunk, eb, want_crc=True)
+    pad = np.zeros(((enc["stream"].size + 31) // 16) * 16, np.uint8)
+    pad[:enc["stream"].size] = enc["stream"]
+    return HostCompressed(ct, x.size, chunk, eb, 1, 0, 0, torch.from_numpy(pad),
+                          torch.from_numpy(enc["offsets"].astype(np.int64)), torch.from_numpy(enc["chunk_min"]),
+                          torch.from_numpy(enc["chunk_medium"]), torch.from_numpy(enc["chunk_type"]),
+                          torch.from_numpy(enc["chunk_crc"].view(np.int32).copy())), enc
+
+
+def crc_chunks(stream, offsets):
+    s, o = stream.numpy(), offsets.numpy()
+    return torch.from_numpy(np.array([ol.o_crc32(s[o[c]:o[c + 1]]) for c in range(o.size - 1)], dtype=np.uint32).view(np.int32))
+
+
+def test_shard_range_partitions_chunks():
+    for n, chunk in ((1 << 20, 4096), (20000, 4096), (4096 * 7 + 5, 4096), (100, 4096), (1 << 16, 0)):
+        for world in (1, 2, 4, 8):
+            pieces = [tr.shard_range(n, chunk, r, world) for r in range(world)]
+            assert pieces[0][0] == 0 and pieces[-1][1] == n
+            for (a0, a1), (b0, b1) in zip(pieces, pieces[1:]):
+                assert a1 == b0 and a0 <= a1
+            if chunk and chunk < n:
+                assert all(lo % chunk == 0 for lo, _ in pieces)
+
+
+def test_sharded_compress_equals_whole():
+    """Chunks are independent: the per-rank streams concatenated are the whole-array stream."""
+    x = make_field("noisy", 4096 * 13 + 100)
+    whole = ol.o_compress_chunked(5, x, 4096, 0.01)
+    for world in (2, 4):
+        parts = []
+        for r in range(world):
+            lo, hi = tr.shard_range(x.size, 4096, r, world)
+            parts.append(ol.o_compress_chunked(5, x[lo:hi], 4096, 0.01)["stream"])
+        assert np.array_equal(np.concatenate(parts), whole["stream"])
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        dev = torch.device("cpu")
+        n, chunk, eb = 4096 * 5 + 77, 4096, 0.01
+        x = make_field("smooth", n, start=1000 * rank)
+        peer = 1 - rank
+        # ---- plain hop (impl/pingpong.c:250 / :353), both directions -------------------------------------------------
+        for ct in (5, 7):
+            comp, enc = oracle_compressed(x, ct, chunk, eb)
+            if rank == 0:
+                tr.send_compressed(comp, peer)
+                got = tr.recv_compressed(n, chunk, peer, dev, HostCompressed)
+            else:
+                got = tr.recv_compressed(n, chunk, peer, dev, HostCompressed)
+                tr.send_compressed(comp, peer)
+            xp = make_field("smooth", n, start=1000 * peer)
+            want, wenc = oracle_compressed(xp, ct, chunk, eb)
+            total = int(got.chunk_offsets[-1])
+            assert (got.ct, got.n, got.chunk_elems, got.abs_error_bound) == (ct, n, chunk, eb)
+            assert torch.equal(got.chunk_offsets, want.chunk_offsets)
+            assert np.array_equal(got.stream[:total].numpy(), wenc["stream"])
+            assert torch.equal(got.chunk_min.view(torch.int32), want.chunk_min.view(torch.int32))
+            assert torch.equal(got.chunk_type, want.chunk_type) and torch.equal(got.chunk_crc, want.chunk_crc)
+            dec = ol.o_decompress_chunked(ct, dict(stream=got.stream[:total].numpy(), offsets=got.chunk_offsets.numpy().astype(np.uint64),
+                                                   chunk_min=got.chunk_min.numpy(), chunk_medium=got.chunk_medium.numpy(),
+                                                   chunk_type=got.chunk_type.numpy()), n, chunk, eb)
+            assert np.array_equal(dec.view(np.uint32), ol.o_decompress_chunked(ct, wenc, n, chunk, eb).view(np.uint32))
+        # ---- CT=8 hop with a corrupted first delivery: one resend (impl/pingpong.c:363-410) -----------------------------
+        comp, enc = oracle_compressed(x, 8, chunk, eb)
+
+        def corrupt(got, attempt):
+            if attempt == 0:
+                got.stream[5] ^= 0x10                         # the reference's bit_flip on the received buffer
+
+        got, resends = tr.pingpong_hop_crc(comp, peer, rank == 0, n, chunk, dev, HostCompressed, crc_chunks,
+                                           corrupt_fn=corrupt if rank == 1 else None)
+        assert resends == 1
+        if rank == 1:
+            x0 = make_field("smooth", n, start=0)
+            assert np.array_equal(got.stream[:int(got.chunk_offsets[-1])].numpy(), oracle_compressed(x0, 8, chunk, eb)[1]["stream"])
+        q.put((rank, "ok"))
+    except Exception as e:  # pragma: no cover
+        import traceback
+        q.put((rank, "FAIL: %s\n%s" % (e, traceback.format_exc())))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_frames_over_gloo_world2():
+    import torch.multiprocessing as mp
+    ol.build_oracle()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(r[1] == "ok" for r in res), res
