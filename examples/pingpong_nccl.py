@@ -3,7 +3,7 @@
 transport.send_compressed / recv_compressed, and the CT=8/9 CRC + ack + resend protocol of :260-289, :363-447).
 
   python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
-      examples/pingpong_nccl.py [--ct 5] [--n 131072] [--eb 0.01] [--hops 100] [--check]
+      examples/pingpong_nccl.py [--ct 5] [--elems 131072] [--eb 0.01] [--hops 100] [--check]
 
 Rank 0 compresses once (as the reference does, impl/pingpong.c:164-169), the compressed frame bounces `hops` times,
 the last receiver decompresses.  --check compares the final floats with the CPU oracle (test infrastructure)."""
@@ -25,7 +25,7 @@ from data_compression_b200.fields import make_field             # noqa: E402
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ct", type=int, default=5)
-    ap.add_argument("--n", type=int, default=131072)             # float_eq_131072 shape (BASELINE.json configs[0])
+    ap.add_argument("--elems", dest="n", type=int, default=131072)             # float_eq_131072 shape (BASELINE.json configs[0])
     ap.add_argument("--eb", type=float, default=0.01)
     ap.add_argument("--chunk", type=int, default=4096)
     ap.add_argument("--hops", type=int, default=100)
