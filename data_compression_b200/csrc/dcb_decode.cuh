@@ -29,65 +29,67 @@ __device__ __forceinline__ void dec_cp_async16(uint32_t smem_dst, const void* gs
   asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"(smem_dst), "l"(gsrc) : "memory");
 }
 __device__ __forceinline__ void dec_cp_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-__device__ __forceinline__ void dec_cp_wait7() { asm volatile("cp.async.wait_group 7;\n" ::: "memory"); }
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
   uint32_t v;
   asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(v) : "r"(addr) : "memory");
   return v;
 }
 
-// Per-lane MSB-first bit reader over a shared-memory ring fed by cp.async.
-// Invariant between codes: 32 <= avail <= 63, `hi` = the next 32 stream bits.
+// Per-lane MSB-first bit reader over a shared-memory ring fed by cp.async.  State on the decode chain: the bit
+// position and a two-word register window (w0:w1); the word after the window is read from the ring one code ahead
+// of its use, so no shared-memory latency sits on the chain.  Everything is branch free.  The ring is topped up
+// once per ROUND of 8 codes with predicated copies, so the copy logic is warp-synchronous instead of firing
+// whenever any lane crosses a block.
 struct LaneReader {
-  uint32_t hi, lo;        // bit window, top aligned
-  int avail;              // valid bits in hi:lo
-  uint32_t nextw;         // ring word `widx`, already read (memory byte order)
-  uint32_t widx;          // running word index (word 0 = first word of the first 16-byte block fetched)
-  uint32_t ring;          // shared-memory byte address of this lane's ring
-  const uint8_t* gnext;   // next 16-byte block to fetch
-  const uint8_t* gend;    // first block at/after the end of this chunk's stream
+  uint32_t bitpos;        // position of the next stream bit, counted from ring word 0 (= first fetched 16-byte block)
+  uint32_t w0, w1;        // stream words bitpos/32 and bitpos/32 + 1, MSB-first
+  uint32_t w2raw;         // stream word bitpos/32 + 2 as it lies in memory (prefetched)
+  uint32_t ring;          // shared-memory byte address of this lane's ring (8 blocks of 16 B)
+  uint32_t fetched;       // 16-byte blocks issued so far (block b lives in ring slot b & 7)
+  uint32_t nblocks;       // blocks that belong to this chunk's stream
+  const uint8_t* gbase;   // address of block 0
 
-  __device__ __forceinline__ void fetch_block(uint32_t blk) {        // block index -> ring slot blk & 7
-    if (gnext < gend) dec_cp_async16(ring + ((blk & 7u) << 4), gnext);
-    gnext += 16;
-    dec_cp_commit();                                                  // (an empty group keeps the count uniform)
+  __device__ __forceinline__ void fetch_if(bool want) {
+    if (want && fetched < nblocks) dec_cp_async16(ring + ((fetched & 7u) << 4), gbase + ((size_t)fetched << 4));
+    fetched += want ? 1u : 0u;
   }
-  // make `nextw` the word after the current one; crossing into a new 16-byte block recycles the block just left
-  __device__ __forceinline__ void advance_word() {
-    widx++;
-    if ((widx & 3u) == 0u) {
-      fetch_block((widx >> 2) + 7u);
-      dec_cp_wait7();                                                 // all but the 7 newest copies done: block widx/4 landed
-    }
-    nextw = lds32(ring + ((widx & (DEC_RING_WORDS - 1u)) << 2));
+  // Called once per round (<= 8 codes, <= 32 bytes consumed since the last call): keep 7 blocks ahead of the current one
+  // in flight; a block is recycled only after the position has left it.  One commit per call, so "all but the two
+  // newest groups" always covers every block the coming round can touch.
+  __device__ __forceinline__ void top_up() {
+    const uint32_t want_until = (bitpos >> 7) + 8u;                  // blocks cur .. cur+7
+    fetch_if(fetched < want_until);
+    fetch_if(fetched < want_until);
+    fetch_if(fetched < want_until);
+    dec_cp_commit();
+    asm volatile("cp.async.wait_group 2;\n" ::: "memory");
   }
-  __device__ __forceinline__ void refill() {
-    if (avail < 32) {
-      const uint32_t w = __byte_perm(nextw, 0u, 0x0123);              // memory order -> MSB-first word
-      hi |= w >> avail;
-      lo = __funnelshift_r(0u, w, avail);                            // (w:0) >> avail, low half
-      avail += 32;
-      advance_word();
-    }
+  __device__ __forceinline__ uint32_t ring_word(uint32_t word) const {
+    return lds32(ring + ((word & (DEC_RING_WORDS - 1u)) << 2));
   }
-  __device__ __forceinline__ void consume(int L) {                    // drop L (0..32) bits, then restore the invariant
-    hi = __funnelshift_lc(lo, hi, L);
-    lo = __funnelshift_lc(0u, lo, L);
-    avail -= L;
-    refill();
+  __device__ __forceinline__ uint32_t peek() const { return __funnelshift_l(w1, w0, bitpos); }   // next 32 bits
+  __device__ __forceinline__ void consume(int L) {                    // L in 0..32: crosses at most one word boundary
+    const uint32_t nb = bitpos + (uint32_t)L;
+    const bool adv = ((nb ^ bitpos) & 32u) != 0u;
+    w0 = adv ? w1 : w0;
+    w1 = adv ? __byte_perm(w2raw, 0u, 0x0123) : w1;
+    bitpos = nb;
+    w2raw = ring_word((nb >> 5) + 2u);                                // same word again when nothing moved
   }
   __device__ __forceinline__ void init(const uint8_t* stream, uint64_t byte_off, uint64_t byte_end, uint32_t ring_addr) {
     ring = ring_addr;
-    gnext = stream + (byte_off & ~15ull);
-    gend = stream + ((byte_end + 15ull) & ~15ull);
+    gbase = stream + (byte_off & ~15ull);
+    nblocks = (uint32_t)((((byte_end + 15ull) & ~15ull) - (byte_off & ~15ull)) >> 4);
+    fetched = 0u;
+    bitpos = (uint32_t)(byte_off & 15ull) * 8u;
     #pragma unroll
-    for (uint32_t b = 0; b < 8u; b++) fetch_block(b);
-    dec_cp_wait7();
-    widx = (uint32_t)(byte_off & 15ull) >> 2;
-    nextw = lds32(ring + (widx << 2));
-    hi = 0u; lo = 0u; avail = 0;
-    refill();                                                         // 32 bits
-    consume((int)(byte_off & 3ull) * 8);                              // sub-word start (chunks are byte aligned)
+    for (int b = 0; b < 8; b++) fetch_if(true);
+    dec_cp_commit();
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    const uint32_t wi = bitpos >> 5;
+    w0 = __byte_perm(ring_word(wi), 0u, 0x0123);
+    w1 = __byte_perm(ring_word(wi + 1u), 0u, 0x0123);
+    w2raw = ring_word(wi + 2u);
   }
 };
 
@@ -119,7 +121,8 @@ __device__ __forceinline__ void decode_fallback(uint32_t w, const CodecConst& k,
 template <int CT>
 __device__ __forceinline__ float decode_one_exact(LaneReader& br, const CodecConst& k, int type, uint32_t ones,
                                                   uint32_t mask17, int m_mask, float& b3, float& b2, float& b1, bool& bad) {
-  const uint32_t w = br.hi;
+  br.top_up();
+  const uint32_t w = br.peek();
   float v; int len;
   if ((w >> 31) && CT != CT_NP) {                                   // 3-bit code (:2965-2967)
     len = 3;
@@ -139,13 +142,83 @@ __device__ __forceinline__ float decode_one_exact(LaneReader& br, const CodecCon
   return v;
 }
 
+// one round: DEC_RND codes of one lane -> v[] (before the min is added back)
 template <int CT>
-__global__ void __launch_bounds__(DEC_NT) dcb_decode_kernel(const DecArgs a) {
+__device__ __forceinline__ void decode_round(LaneReader& br, const CodecConst& k, int type, uint32_t ones, uint32_t mask17,
+                                             int m_mask, float& b3, float& b2, float& b1, bool& bad, float (&v)[DEC_RND]) {
+  bool done = false;
+  br.top_up();
+  if (CT != CT_NP) {
+    // fast round: the next 8 codes all start with 1 (3-bit codes) and b1 holds a value
+    const uint32_t w = br.peek();
+    if (b1 != -1.0f && (w & 0x92492400u) == 0x92492400u) {
+      float c1 = b1, c2 = b2, c3 = b3;
+      float t1 = __fmul_rn(3.0f, c1), t2 = __fmul_rn(3.0f, c2);
+      uint32_t neg = 0u;
+      #pragma unroll
+      for (int e = 0; e < DEC_RND; e++) {
+        const float p2 = __fsub_rn(__fadd_rn(c1, c1), c2);          // 2*b1 is exact: same as __fmul_rn(2, b1)
+        const float p3 = __fadd_rn(__fsub_rn(t1, t2), c3);
+        const bool bb = (w & (0x20000000u >> (3 * e))) != 0u;
+        const bool ba = (w & (0x40000000u >> (3 * e))) != 0u;
+        const float lo2 = bb ? c1 : 0.0f;
+        const float hi2 = bb ? p3 : p2;
+        const float x = ba ? hi2 : lo2;
+        v[e] = x;
+        neg |= f2u(x);
+        c3 = c2; c2 = c1; c1 = x;
+        t2 = t1; t1 = __fmul_rn(3.0f, x);
+      }
+      if (!(neg >> 31)) {                  // no negative value -> none is the -1.0f marker: commit
+        b1 = c1; b2 = c2; b3 = c3;
+        br.consume(3 * DEC_RND);
+        done = true;
+      }
+    }
+  }
+  if (!done) {
+    // general round, branch free.  History update == hist_push (:3110-3127) given b3, b2 != -1.0f:
+    // a -1.0f in b1 is overwritten instead of shifted out.
+    #pragma unroll
+    for (int e = 0; e < DEC_RND; e++) {
+      const uint32_t w = br.peek();
+      uint32_t vb; int len;
+      decode_fallback<CT>(w, k, type, ones, mask17, m_mask, vb, len);
+      float x = u2f(vb);
+      if (CT == CT_NP) {
+        bad |= (w >> 31) != 0u;                                     // :2501-2505 "Error leading bit 1"
+      } else {
+        const bool is3 = (w >> 31) != 0u;
+        const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);
+        const float p3 = __fadd_rn(__fsub_rn(__fmul_rn(3.0f, b1), __fmul_rn(3.0f, b2)), b3);
+        const bool bb = (w & 0x20000000u) != 0u, ba = (w & 0x40000000u) != 0u;
+        const float x3 = ba ? (bb ? p3 : p2) : (bb ? b1 : 0.0f);    // decompress_bitwise_float :3139-3158
+        x = is3 ? x3 : x;
+        len = is3 ? 3 : len;
+        const bool shift_ok = (b1 != -1.0f);
+        b3 = shift_ok ? b2 : b3;
+        b2 = shift_ok ? b1 : b2;
+        b1 = x;
+      }
+      v[e] = x;
+      br.consume(len);
+    }
+  }
+}
+
+#define DEC_SUPER 32                // codes per lane between two coalesced write-outs
+#define DEC_OPITCH 36               // floats per lane row of the output staging (144 B: conflict-free 128-bit accesses)
+
+template <int CT>
+__global__ void __launch_bounds__(DEC_NT, 8) dcb_decode_kernel(const DecArgs a) {
   __shared__ __align__(16) uint32_t rings[DEC_NT * DEC_PITCH];
-  const uint64_t c = (uint64_t)blockIdx.x * DEC_NT + threadIdx.x;
-  if (c >= a.num_chunks) return;
+  __shared__ __align__(16) float ostage[DEC_NT * DEC_OPITCH];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint64_t c_raw = (uint64_t)blockIdx.x * DEC_NT + threadIdx.x;
+  const bool active = c_raw < a.num_chunks;
+  const uint64_t c = active ? c_raw : 0ull;                        // idle lanes shadow chunk 0 but never store
   const uint64_t elem0 = c * a.chunk;
-  const uint32_t cn = (uint32_t)min(a.chunk, a.n - elem0);
+  const uint32_t cn = active ? (uint32_t)min(a.chunk, a.n - elem0) : 0u;
   const bool addmin = (a.flags & 1u) != 0;
   const float mn = (addmin && a.cmin) ? a.cmin[c] : 0.0f;
   int type = a.fixed_type;
@@ -160,6 +233,9 @@ __global__ void __launch_bounds__(DEC_NT) dcb_decode_kernel(const DecArgs a) {
           (uint32_t)__cvta_generic_to_shared(rings + threadIdx.x * DEC_PITCH));
   float* out = a.out + elem0;
   const bool vec_ok = ((reinterpret_cast<uintptr_t>(out) & 31) == 0);
+  // coalesced write-out needs the whole warp on full chunks and 128-byte aligned rows
+  const bool coop = __all_sync(0xffffffffu, active && cn == (uint32_t)a.chunk) && (a.chunk % DEC_SUPER) == 0 &&
+                    ((reinterpret_cast<uintptr_t>(a.out) & 127) == 0);
 
   float b3 = -1.0f, b2 = -1.0f, b1 = -1.0f;                         // :2930
   bool bad = false;
@@ -173,65 +249,12 @@ __global__ void __launch_bounds__(DEC_NT) dcb_decode_kernel(const DecArgs a) {
       i++;
     }
   }
-  for (; i + DEC_RND <= cn; i += DEC_RND) {
+  // ---- rounds with per-lane sector stores: up to a DEC_SUPER boundary common to the warp (coop) or to the end -------
+  uint32_t direct_end = cn;
+  if (coop) direct_end = min(cn, __reduce_max_sync(0xffffffffu, (i + DEC_SUPER - 1u) & ~(uint32_t)(DEC_SUPER - 1u)));
+  for (; i + DEC_RND <= direct_end; i += DEC_RND) {
     float v[DEC_RND];
-    bool done = false;
-    if (CT != CT_NP) {
-      // fast round: the next 8 codes all start with 1 (3-bit codes) and b1 holds a value
-      if (b1 != -1.0f && (br.hi & 0x92492400u) == 0x92492400u) {
-        const uint32_t w = br.hi;
-        float c1 = b1, c2 = b2, c3 = b3;
-        float t1 = __fmul_rn(3.0f, c1), t2 = __fmul_rn(3.0f, c2);
-        uint32_t neg = 0u;
-        #pragma unroll
-        for (int e = 0; e < DEC_RND; e++) {
-          const float p2 = __fsub_rn(__fadd_rn(c1, c1), c2);          // 2*b1 is exact: same as __fmul_rn(2, b1)
-          const float p3 = __fadd_rn(__fsub_rn(t1, t2), c3);
-          const bool bb = (w & (0x20000000u >> (3 * e))) != 0u;
-          const bool ba = (w & (0x40000000u >> (3 * e))) != 0u;
-          const float lo2 = bb ? c1 : 0.0f;
-          const float hi2 = bb ? p3 : p2;
-          const float x = ba ? hi2 : lo2;
-          v[e] = x;
-          neg |= f2u(x);
-          c3 = c2; c2 = c1; c1 = x;
-          t2 = t1; t1 = __fmul_rn(3.0f, x);
-        }
-        if (!(neg >> 31)) {                  // no negative value -> none is the -1.0f marker: commit
-          b1 = c1; b2 = c2; b3 = c3;
-          br.consume(3 * DEC_RND);
-          done = true;
-        }
-      }
-    }
-    if (!done) {
-      // general round, branch free.  History update == hist_push (:3110-3127) given b3, b2 != -1.0f:
-      // a -1.0f in b1 is overwritten instead of shifted out.
-      #pragma unroll
-      for (int e = 0; e < DEC_RND; e++) {
-        const uint32_t w = br.hi;
-        uint32_t vb; int len;
-        decode_fallback<CT>(w, a.k, type, ones, mask17, m_mask, vb, len);
-        float x = u2f(vb);
-        if (CT == CT_NP) {
-          bad |= (w >> 31) != 0u;                                     // :2501-2505 "Error leading bit 1"
-        } else {
-          const bool is3 = (w >> 31) != 0u;
-          const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);
-          const float p3 = __fadd_rn(__fsub_rn(__fmul_rn(3.0f, b1), __fmul_rn(3.0f, b2)), b3);
-          const bool bb = (w & 0x20000000u) != 0u, ba = (w & 0x40000000u) != 0u;
-          const float x3 = ba ? (bb ? p3 : p2) : (bb ? b1 : 0.0f);    // decompress_bitwise_float :3139-3158
-          x = is3 ? x3 : x;
-          len = is3 ? 3 : len;
-          const bool shift_ok = (b1 != -1.0f);
-          b3 = shift_ok ? b2 : b3;
-          b2 = shift_ok ? b1 : b2;
-          b1 = x;
-        }
-        v[e] = x;
-        br.consume(len);
-      }
-    }
+    decode_round<CT>(br, a.k, type, ones, mask17, m_mask, b3, b2, b1, bad, v);
     if (addmin) {
       #pragma unroll
       for (int e = 0; e < DEC_RND; e++) v[e] = __fadd_rn(v[e], mn);  // decompressed[i] + min, impl/pingpong.c:562
@@ -244,6 +267,41 @@ __global__ void __launch_bounds__(DEC_NT) dcb_decode_kernel(const DecArgs a) {
       #pragma unroll
       for (int e = 0; e < DEC_RND; e++) out[i + e] = v[e];
     }
+  }
+  if (coop) {
+    // ---- super-rounds: every lane decodes 32 codes into its staging row; the warp then writes 32 rows of 128 B,
+    //      four rows per 128-bit store instruction (one L1 wavefront per row instead of eight per lane).
+    //      i is the same in every lane here and cn == chunk, so the loop is warp uniform.
+    float* row = ostage + threadIdx.x * DEC_OPITCH;
+    const float* wbase = ostage + warp * 32 * DEC_OPITCH;
+    float* wout = a.out + ((uint64_t)blockIdx.x * DEC_NT + (uint64_t)warp * 32) * a.chunk;
+    for (; i + DEC_SUPER <= cn; i += DEC_SUPER) {
+      #pragma unroll
+      for (int r = 0; r < DEC_SUPER / DEC_RND; r++) {
+        float v[DEC_RND];
+        decode_round<CT>(br, a.k, type, ones, mask17, m_mask, b3, b2, b1, bad, v);
+        if (addmin) {
+          #pragma unroll
+          for (int e = 0; e < DEC_RND; e++) v[e] = __fadd_rn(v[e], mn);
+        }
+        *reinterpret_cast<float4*>(row + r * DEC_RND) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(row + r * DEC_RND + 4) = make_float4(v[4], v[5], v[6], v[7]);
+      }
+      __syncwarp();
+      #pragma unroll
+      for (int q = 0; q < 8; q++) {
+        const int rr = 4 * q + (lane >> 3), cc = (lane & 7) * 4;
+        const float4 t = *reinterpret_cast<const float4*>(wbase + rr * DEC_OPITCH + cc);
+        *reinterpret_cast<float4*>(wout + (uint64_t)rr * a.chunk + i + cc) = t;
+      }
+      __syncwarp();
+    }
+  }
+  for (; i + DEC_RND <= cn; i += DEC_RND) {                         // remaining whole rounds, per-lane stores
+    float v[DEC_RND];
+    decode_round<CT>(br, a.k, type, ones, mask17, m_mask, b3, b2, b1, bad, v);
+    #pragma unroll
+    for (int e = 0; e < DEC_RND; e++) out[i + e] = addmin ? __fadd_rn(v[e], mn) : v[e];
   }
   for (; i < cn; i++) {                                              // ragged tail of the last chunk
     const float x = decode_one_exact<CT>(br, a.k, type, ones, mask17, m_mask, b3, b2, b1, bad);
