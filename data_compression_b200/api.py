@@ -15,7 +15,7 @@ from typing import Optional
 import numpy as np
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "libdcb200.so")
+LIB_PATH = os.environ.get("DCB200_LIB") or os.path.join(PKG, "libdcb200.so")   # override: A/B builds of the same ABI
 
 CT_BITWISE, CT_BITWISE_NP, CT_BITWISE_MASK, CT_BITWISE_CRC, CT_MASK_CRC, CT_BITWISE_OP = 5, 6, 7, 8, 9, 11
 F_SUBTRACT_MIN, F_FIXED_MASK, F_CRC, F_EXACT_MEDIUM = 1, 2, 4, 8
