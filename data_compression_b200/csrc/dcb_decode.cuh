@@ -46,9 +46,10 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
 // once per ROUND of 8 codes with predicated copies, so the copy logic is warp-synchronous instead of firing
 // whenever any lane crosses a block.
 struct LaneReader {
-  uint32_t bitpos;        // position of the next stream bit, counted from ring word 0 (= first fetched 16-byte block)
-  uint32_t w0, w1;        // stream words bitpos/32 and bitpos/32 + 1, MSB-first
-  uint32_t w2raw;         // stream word bitpos/32 + 2 as it lies in memory (prefetched)
+  uint32_t pos;           // position of the next stream bit counted from ring word 0, PLUS 64: with the bias, pos >> 5 is the
+                          // ring word right after the two-word window, and everything else only needs pos mod 32 / bit 5
+  uint32_t w0, w1;        // stream words at the position and after it, MSB-first
+  uint32_t w2raw;         // the word after the window as it lies in memory (prefetched one code ahead)
   uint32_t ring;          // shared-memory byte address of this lane's ring (8 blocks of 16 B)
   uint32_t fetched;       // 16-byte blocks issued so far (block b lives in ring slot b & 7)
   uint32_t nblocks;       // blocks that belong to this chunk's stream
@@ -62,7 +63,7 @@ struct LaneReader {
   // in flight; a block is recycled only after the position has left it.  One commit per call, so "all but the two
   // newest groups" always covers every block the coming round can touch.
   __device__ __forceinline__ void top_up() {
-    const uint32_t want_until = (bitpos >> 7) + 8u;                  // blocks cur .. cur+7
+    const uint32_t want_until = ((pos - 64u) >> 7) + 8u;             // blocks cur .. cur+7
     fetch_if(fetched < want_until);
     fetch_if(fetched < want_until);
     fetch_if(fetched < want_until);
@@ -72,25 +73,22 @@ struct LaneReader {
   __device__ __forceinline__ uint32_t ring_word(uint32_t word) const {
     return lds32(ring + ((word & (DEC_RING_WORDS - 1u)) << 2));
   }
-  __device__ __forceinline__ uint32_t peek() const { return __funnelshift_l(w1, w0, bitpos); }   // next 32 bits
+  __device__ __forceinline__ uint32_t peek() const { return __funnelshift_l(w1, w0, pos); }      // next 32 bits
   __device__ __forceinline__ void consume(int L) {                    // L in 0..32: crosses at most one word boundary
-    const uint32_t nb = bitpos + (uint32_t)L;
-    const bool adv = ((nb ^ bitpos) & 32u) != 0u;
+    const uint32_t np = pos + (uint32_t)L;
+    const bool adv = ((np ^ pos) & 32u) != 0u;
     w0 = adv ? w1 : w0;
     w1 = adv ? __byte_perm(w2raw, 0u, 0x0123) : w1;
-    bitpos = nb;
-#if DEC_EXP == 1
-    w2raw = nb * 2654435761u;
-#else
-    w2raw = ring_word((nb >> 5) + 2u);                                // same word again when nothing moved
-#endif
+    pos = np;
+    w2raw = lds32(ring + ((np >> 3) & ((DEC_RING_WORDS - 1u) << 2)));  // word (np >> 5) & 31: the same one when nothing moved
   }
   __device__ __forceinline__ void init(const uint8_t* stream, uint64_t byte_off, uint64_t byte_end, uint32_t ring_addr) {
     ring = ring_addr;
     gbase = stream + (byte_off & ~15ull);
     nblocks = (uint32_t)((((byte_end + 15ull) & ~15ull) - (byte_off & ~15ull)) >> 4);
     fetched = 0u;
-    bitpos = (uint32_t)(byte_off & 15ull) * 8u;
+    const uint32_t bitpos = (uint32_t)(byte_off & 15ull) * 8u;
+    pos = bitpos + 64u;
     #pragma unroll
     for (int b = 0; b < 8; b++) fetch_if(true);
     dec_cp_commit();
@@ -107,9 +105,9 @@ template <int CT>
 __device__ __forceinline__ void decode_fallback(uint32_t w, const CodecConst& k, int type, uint32_t ones, uint32_t mask17,
                                                 int m_mask, uint32_t& vbits, int& len) {
   if (CT == CT_OP) { len = 32; vbits = w; return; }                 // :718-721
-  const int sh = min(max(150 - k.n_eb - (int)(w >> 23), 0), 23);    // leading bit 0: w >> 23 is the exponent field
-  len = 32 - sh;
-  vbits = (w & (0xFFFFFFFFu << sh)) | ((1u << sh) >> 1);            // top `len` bits, then a single 1, then zeros
+  // leading bit 0: w >> 23 is the exponent field.  (A leading 1 gives len 32: callers that accept 3-bit codes subtract 29.)
+  len = min(max((int)(w >> 23) + k.n_eb_m118, 9), 32);              // 9 + m, m = clamp(n_eb + E - 127, 0, 23)
+  vbits = (w & ~__funnelshift_rc(0xFFFFFFFFu, 0u, len)) | __funnelshift_rc(0x80000000u, 0u, len);   // top `len` bits, a 1, zeros
   if (CT == CT_MASK) {
     if (((w >> (31 - type)) & ones) == ones) {                      // 0, `type` ones: escape (:1739-1758)
       const uint32_t flag = (w >> (30 - type)) & 1u;
@@ -186,8 +184,14 @@ __device__ __forceinline__ void decode_round(LaneReader& br, const CodecConst& k
     }
   }
   if (!done) {
-    // general round, branch free.  History update == hist_push (:3110-3127) given b3, b2 != -1.0f:
-    // a -1.0f in b1 is overwritten instead of shifted out.
+    // general round, branch free: any mix of raw / escape / 3-bit codes.
+    //   len: the exponent rule gives 32 for a leading 1, so a 3-bit code is "32 - 29" (one IMAD instead of a select)
+    //   history: b3 <- b2 <- b1 <- x is hist_push (:3110-3127) as long as no slot holds the -1.0f "empty" marker.  The
+    //   round is run assuming that (pure register renaming), remembering whether a decoded value was exactly -1.0f;
+    //   if one was, or b1 holds the marker on entry, the reader is rewound and the round is redone with the exact update.
+    const LaneReader br0 = br;
+    const float s1 = b1, s2 = b2, s3 = b3;
+    bool marker = (CT != CT_NP) && (b1 == -1.0f);
     #pragma unroll
     for (int e = 0; e < DEC_RND; e++) {
       const uint32_t w = br.peek();
@@ -196,7 +200,8 @@ __device__ __forceinline__ void decode_round(LaneReader& br, const CodecConst& k
       float x = u2f(vb);
       if (CT == CT_NP) {
         bad |= (w >> 31) != 0u;                                     // :2501-2505 "Error leading bit 1"
-      } else {
+      } else if (CT == CT_OP || CT == CT_MASK) {
+        // (CT_OP: 32-bit words; CT_MASK: escape lengths do not follow the exponent rule) -> plain select
         const bool is3 = (w >> 31) != 0u;
         const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);
         const float p3 = __fadd_rn(__fsub_rn(__fmul_rn(3.0f, b1), __fmul_rn(3.0f, b2)), b3);
@@ -204,13 +209,30 @@ __device__ __forceinline__ void decode_round(LaneReader& br, const CodecConst& k
         const float x3 = ba ? (bb ? p3 : p2) : (bb ? b1 : 0.0f);    // decompress_bitwise_float :3139-3158
         x = is3 ? x3 : x;
         len = is3 ? 3 : len;
-        const bool shift_ok = (b1 != -1.0f);
-        b3 = shift_ok ? b2 : b3;
-        b2 = shift_ok ? b1 : b2;
-        b1 = x;
+        marker |= (x == -1.0f);
+        b3 = b2; b2 = b1; b1 = x;
+      } else {
+        const uint32_t is3 = w >> 31;
+        const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);
+        const float p3 = __fadd_rn(__fsub_rn(__fmul_rn(3.0f, b1), __fmul_rn(3.0f, b2)), b3);
+        const bool bb = (w & 0x20000000u) != 0u, ba = (w & 0x40000000u) != 0u;
+        const float x3 = ba ? (bb ? p3 : p2) : (bb ? b1 : 0.0f);    // decompress_bitwise_float :3139-3158
+        x = is3 ? x3 : x;
+        len -= 29 * (int)is3;
+        marker |= (x == -1.0f);
+        b3 = b2; b2 = b1; b1 = x;
       }
       v[e] = x;
       br.consume(len);
+    }
+    if (CT != CT_NP && marker) {                                    // rare: redo with the exact state machine
+      br = br0; b1 = s1; b2 = s2; b3 = s3;
+      #pragma unroll 1
+      for (int e = 0; e < DEC_RND; e++) {
+        const float x = decode_one_exact<CT>(br, k, type, ones, mask17, m_mask, b3, b2, b1, bad);
+        #pragma unroll
+        for (int j = 0; j < DEC_RND; j++) v[j] = (j == e) ? x : v[j];
+      }
     }
   }
 }
@@ -219,7 +241,7 @@ __device__ __forceinline__ void decode_round(LaneReader& br, const CodecConst& k
 #define DEC_OPITCH 36               // floats per lane row of the output staging (144 B: conflict-free 128-bit accesses)
 
 template <int CT>
-__global__ void __launch_bounds__(DEC_NT, 8) dcb_decode_kernel(const DecArgs a) {
+__global__ void __launch_bounds__(DEC_NT, 6) dcb_decode_kernel(const DecArgs a) {
   __shared__ __align__(16) uint32_t rings[DEC_NT * DEC_PITCH];
   __shared__ __align__(16) float ostage[DEC_NT * DEC_OPITCH];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
