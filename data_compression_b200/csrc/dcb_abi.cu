@@ -1,6 +1,13 @@
 // dcb_abi.cu -- extern "C" entry points of libdcb200.so (include/dc_b200.h).
 // Host logic only: argument checks, error-bound constants, launch configuration.  No CPU codec lives
 // here: without a CUDA device every entry point returns DCB_ENODEVICE.
+#include <atomic>
+#include <thread>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
 #include "../../include/dc_b200.h"
 #include "dcb_common.cuh"
 #include "dcb_encode.cuh"
@@ -262,6 +269,8 @@ struct HostCtx {
   cudaStream_t st = nullptr;
   void* buf[8] = {nullptr};
   size_t cap[8] = {0};
+  char* pin = nullptr;            // pinned staging for the chunk tables: the caller's table pointers may be pageable, and the
+  size_t pin_cap = 0;             // driver's pageable-copy path serialises against the bulk copies of other host threads
 };
 static thread_local HostCtx g_h;
 static thread_local uint64_t g_last_bits = 0;
@@ -276,6 +285,42 @@ static int hbuf(int i, size_t bytes, void** p) {
     g_h.cap[i] = bytes;
   }
   *p = g_h.buf[i];
+  return DCB_OK;
+}
+// Host <-> device transfers of the host-pointer layer.  A copy engine serves the streams that feed it one after the other
+// (measured: a 100 MB copy queued behind another host thread's 1 GB copy in the same direction waits for all of it, even
+// when that copy is issued in small slices), which leaves the opposite direction idle whenever two host threads overlap
+// a compress with a decompress.  So every transfer goes out in slices, and a slice holds a FAIR per-direction lock
+// until it has completed: concurrent callers alternate slice by slice, and both engines stay busy.
+struct TicketLock {
+  std::atomic<uint64_t> next{0}, serving{0};
+  void lock() { const uint64_t t = next.fetch_add(1, std::memory_order_relaxed);
+                while (serving.load(std::memory_order_acquire) != t) std::this_thread::yield(); }
+  void unlock() { serving.fetch_add(1, std::memory_order_release); }
+};
+static TicketLock g_h2d_mu, g_d2h_mu;
+static const bool g_trace = getenv("DCB_TRACE") != nullptr;
+static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+#define TRACE(what) do { if (g_trace) fprintf(stderr, "[dcb %p] %-28s %.2f\n", (void*)&g_h, what, now_ms()); } while (0)
+static cudaError_t copy_sliced(TicketLock& mu, void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t st) {
+  static const size_t SL = [] { const char* e = getenv("DCB_COPY_SLICE_MB"); long v = e ? atol(e) : 32; return v > 0 ? (size_t)v << 20 : ~(size_t)0 >> 1; }();
+  cudaError_t e = cudaStreamSynchronize(st);           // whatever produces the source runs outside the lock
+  for (size_t o = 0; o < bytes && e == cudaSuccess; o += SL) {
+    mu.lock();
+    e = cudaMemcpyAsync((char*)dst + o, (const char*)src + o, bytes - o < SL ? bytes - o : SL, kind, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    mu.unlock();
+  }
+  return e;
+}
+static int pinbuf(size_t bytes, char** p) {
+  if (g_h.pin_cap < bytes) {
+    if (g_h.pin) cudaFreeHost(g_h.pin);
+    g_h.pin = nullptr; g_h.pin_cap = 0;
+    CK(cudaHostAlloc((void**)&g_h.pin, bytes, cudaHostAllocDefault));
+    g_h.pin_cap = bytes;
+  }
+  *p = g_h.pin;
   return DCB_OK;
 }
 #define HB(i, bytes, ptr) do { int rc_ = hbuf(i, bytes, (void**)&(ptr)); if (rc_) return rc_; } while (0)
@@ -294,24 +339,37 @@ extern "C" int dcb_compress_host(int ct, const float* h_in, uint64_t n, uint64_t
   HB(0, n * 4, d_in); HB(1, dcb_max_stream_bytes(n, chunk), d_s); HB(2, (K + 1) * 8, d_off);
   HB(3, K * 4, d_min); HB(4, K * 4, d_med); HB(5, K * 4, d_ty); HB(6, K * 4, d_crc);
   HB(7, dcb_workspace_bytes(n, chunk), d_ws);
-  CK(cudaMemcpyAsync(d_in, h_in, n * 4, cudaMemcpyHostToDevice, st));
+  TRACE("C: begin");
+  CK(copy_sliced(g_h2d_mu, d_in, h_in, n * 4, cudaMemcpyHostToDevice, st));
+  TRACE("C: input in");
   uint32_t f2 = flags;
   const int bct = base_ct(ct, &f2);
   int rc = dcb_compress(ct, d_in, n, chunk, eb, flags, fixed_type, fixed_mask17, d_s, dcb_max_stream_bytes(n, chunk),
                         d_off, d_min, d_med, d_ty, d_crc, d_ws, dcb_workspace_bytes(n, chunk), st);
   if (rc) return rc;
-  CK(cudaMemcpyAsync(h_offsets, d_off, (K + 1) * 8, cudaMemcpyDeviceToHost, st));
-  if (h_cmin) CK(cudaMemcpyAsync(h_cmin, d_min, K * 4, cudaMemcpyDeviceToHost, st));
-  if (bct == CT_MASK && !(flags & DCB_F_FIXED_MASK)) {
-    if (h_cmed) CK(cudaMemcpyAsync(h_cmed, d_med, K * 4, cudaMemcpyDeviceToHost, st));
-    if (h_ctype) CK(cudaMemcpyAsync(h_ctype, d_ty, K * 4, cudaMemcpyDeviceToHost, st));
-  }
-  if ((f2 & DCB_F_CRC) && h_ccrc) CK(cudaMemcpyAsync(h_ccrc, d_crc, K * 4, cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(&g_last_bits, (char*)d_ws + 8, 8, cudaMemcpyDeviceToHost, st));
+  char* pin; { int rc_ = pinbuf((K + 1) * 8 + 4 * K * 4 + 64, &pin); if (rc_) return rc_; }
+  uint64_t* p_off = (uint64_t*)pin;
+  char* p_tab = pin + (K + 1) * 8;                          // min | medium | type | crc | last_bits
+  const bool want_mask = (bct == CT_MASK && !(flags & DCB_F_FIXED_MASK));
+  const bool want_crc = (f2 & DCB_F_CRC) && h_ccrc;
+  CK(cudaMemcpyAsync(p_off, d_off, (K + 1) * 8, cudaMemcpyDeviceToHost, st));
+  if (h_cmin) CK(cudaMemcpyAsync(p_tab, d_min, K * 4, cudaMemcpyDeviceToHost, st));
+  if (want_mask && h_cmed) CK(cudaMemcpyAsync(p_tab + K * 4, d_med, K * 4, cudaMemcpyDeviceToHost, st));
+  if (want_mask && h_ctype) CK(cudaMemcpyAsync(p_tab + 2 * K * 4, d_ty, K * 4, cudaMemcpyDeviceToHost, st));
+  if (want_crc) CK(cudaMemcpyAsync(p_tab + 3 * K * 4, d_crc, K * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(p_tab + 4 * K * 4, (char*)d_ws + 8, 8, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));                       // the stream length is only known now
+  TRACE("C: kernel+tables done");
+  memcpy(h_offsets, p_off, (K + 1) * 8);
+  if (h_cmin) memcpy(h_cmin, p_tab, K * 4);
+  if (want_mask && h_cmed) memcpy(h_cmed, p_tab + K * 4, K * 4);
+  if (want_mask && h_ctype) memcpy(h_ctype, p_tab + 2 * K * 4, K * 4);
+  if (want_crc) memcpy(h_ccrc, p_tab + 3 * K * 4, K * 4);
+  memcpy(&g_last_bits, p_tab + 4 * K * 4, 8);
   const uint64_t total = h_offsets[K];
-  if (total) CK(cudaMemcpyAsync(h_stream, d_s, total, cudaMemcpyDeviceToHost, st));
+  if (total) CK(copy_sliced(g_d2h_mu, h_stream, d_s, total, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  TRACE("C: stream out done");
   return DCB_OK;
 }
 
@@ -329,18 +387,23 @@ extern "C" int dcb_decompress_host(int ct, const uint8_t* h_stream, const uint64
   float* d_out; uint8_t* d_s; uint64_t* d_off; float* d_min; float* d_med; int32_t* d_ty; int32_t* d_status; 
   HB(0, n * 4, d_out); HB(1, dcb_max_stream_bytes(n, chunk), d_s); HB(2, (K + 1) * 8, d_off);
   HB(3, K * 4, d_min); HB(4, K * 4, d_med); HB(5, K * 4, d_ty); HB(6, 256, d_status);
-  CK(cudaMemcpyAsync(d_s, h_stream, total, cudaMemcpyHostToDevice, st));
-  CK(cudaMemcpyAsync(d_off, h_offsets, (K + 1) * 8, cudaMemcpyHostToDevice, st));
-  if (h_cmin) CK(cudaMemcpyAsync(d_min, h_cmin, K * 4, cudaMemcpyHostToDevice, st));
-  if (h_cmed) CK(cudaMemcpyAsync(d_med, h_cmed, K * 4, cudaMemcpyHostToDevice, st));
-  if (h_ctype) CK(cudaMemcpyAsync(d_ty, h_ctype, K * 4, cudaMemcpyHostToDevice, st));
+  TRACE("D: begin");
+  CK(copy_sliced(g_h2d_mu, d_s, h_stream, total, cudaMemcpyHostToDevice, st));
+  char* pin; { int rc_ = pinbuf((K + 1) * 8 + 4 * K * 4 + 64, &pin); if (rc_) return rc_; }
+  char* p_tab = pin + (K + 1) * 8;
+  memcpy(pin, h_offsets, (K + 1) * 8);
+  CK(cudaMemcpyAsync(d_off, pin, (K + 1) * 8, cudaMemcpyHostToDevice, st));
+  if (h_cmin) { memcpy(p_tab, h_cmin, K * 4); CK(cudaMemcpyAsync(d_min, p_tab, K * 4, cudaMemcpyHostToDevice, st)); }
+  if (h_cmed) { memcpy(p_tab + K * 4, h_cmed, K * 4); CK(cudaMemcpyAsync(d_med, p_tab + K * 4, K * 4, cudaMemcpyHostToDevice, st)); }
+  if (h_ctype) { memcpy(p_tab + 2 * K * 4, h_ctype, K * 4); CK(cudaMemcpyAsync(d_ty, p_tab + 2 * K * 4, K * 4, cudaMemcpyHostToDevice, st)); }
   int rc = dcb_decompress(ct, d_s, d_off, n, chunk, eb, flags, fixed_type, fixed_mask17,
                           h_cmin ? d_min : nullptr, h_cmed ? d_med : nullptr, h_ctype ? d_ty : nullptr,
                           d_out, d_status, st);
   if (rc) return rc;
-  int32_t status = 0;
-  CK(cudaMemcpyAsync(h_out, d_out, n * 4, cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(&status, d_status, 4, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  return status ? DCB_EFORMAT : DCB_OK;
+  if (g_trace) { cudaStreamSynchronize(st); TRACE("D: stream in + kernel done"); }
+  int32_t* p_status = (int32_t*)(p_tab + 4 * K * 4);
+  CK(cudaMemcpyAsync(p_status, d_status, 4, cudaMemcpyDeviceToHost, st));
+  CK(copy_sliced(g_d2h_mu, h_out, d_out, n * 4, cudaMemcpyDeviceToHost, st));
+  TRACE("D: output out");
+  return *p_status ? DCB_EFORMAT : DCB_OK;
 }

@@ -212,13 +212,12 @@ __device__ __forceinline__ void decode_round(LaneReader& br, const CodecConst& k
         marker |= (x == -1.0f);
         b3 = b2; b2 = b1; b1 = x;
       } else {
-        const uint32_t is3 = w >> 31;
         const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);
         const float p3 = __fadd_rn(__fsub_rn(__fmul_rn(3.0f, b1), __fmul_rn(3.0f, b2)), b3);
-        const bool bb = (w & 0x20000000u) != 0u, ba = (w & 0x40000000u) != 0u;
+        const bool bb = (w & 0x20000000u) != 0u, ba = (w & 0x40000000u) != 0u, is3 = (w & 0x80000000u) != 0u;
         const float x3 = ba ? (bb ? p3 : p2) : (bb ? b1 : 0.0f);    // decompress_bitwise_float :3139-3158
         x = is3 ? x3 : x;
-        len -= 29 * (int)is3;
+        asm("mad.lo.s32 %0, %1, -29, %0;" : "+r"(len) : "r"(w >> 31));   // on the FMA pipe; the ALU pipe is the busy one
         marker |= (x == -1.0f);
         b3 = b2; b2 = b1; b1 = x;
       }

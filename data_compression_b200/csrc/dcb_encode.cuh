@@ -148,6 +148,7 @@ struct EncSmem {
   uint32_t xchg[DCB_NT / 32];        // tail word of every warp's last lane (completes the next warp's first word)
   float hx[2][DCB_NT / 32][4];       // last three RAW values of every warp (look-back of the next warp's lane 0)
   uint32_t tkt[2];                   // prefetched tickets
+  float red_w[2][DCB_NT / 32];       // CT=7: weighted sum for the bracket of the sequential sum
   uint32_t walkmask[DCB_NT / 32];    // exact-sum fallback: threads where the serial walk has to stop
   unsigned long long P;              // absolute bit offset of the tile being copied out
   uint32_t pend_tile[2], pend_bits[2], pend_c[2], pend_last[2];   // tiles packed in the previous two iterations (each is finished two iterations later)
@@ -525,9 +526,31 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
           for (int e = 0; e < DCB_E; e++) ps = __fadd_rn(ps, x[e]);
         }
         if (!slow && !(a.flags & 8u)) {                      // DCB_F_EXACT_MEDIUM skips the shortcut
-          const float S = block_sum_any_order(ps, sm, par, lane, warp);
-          const float rel = (float)(cnt + 64) * (1.02f / 16777216.0f);
-          const float lo = __fmul_rd(S, __fsub_rd(1.0f, rel)), hi = __fmul_ru(S, __fadd_ru(1.0f, rel));
+          // Bracket of the reference's sequential sum S_seq around the tree sum S (all values >= 0, u = 2^-24):
+          //   S_seq = sum(y) + sum(e_i), |e_i| <= u * s_i (round to nearest), s_i <= (1 + 1.001 i u) * P_i, P_i the exact
+          //   prefix, and sum_i P_i = sum_j y_j * (cnt - j): the error bound is u * W with W the WEIGHTED sum -- for an even
+          //   field half of the textbook cnt * u * S, which halves the number of tiles that need the exact walk.
+          //   W is accumulated rounding up; 1.02 covers the (1 + 1.001 cnt u) factor and the reduction tree's own
+          //   roundings (<= 13 adds); the tree sum itself is within 32 u of sum(y): 64 u * S with slack.
+          float pw = 0.0f;
+          {
+            float wf = (float)(cnt - tid * DCB_E);            // weights past the end multiply zero padding: their sign is irrelevant
+            #pragma unroll
+            for (int e = 0; e < DCB_E; e++) { pw = __fmaf_ru(x[e], wf, pw); wf = __fsub_rn(wf, 1.0f); }
+          }
+          float S = ps, Wt = pw;
+          #pragma unroll
+          for (int o = 16; o; o >>= 1) {
+            S = __fadd_rn(S, __shfl_xor_sync(0xffffffffu, S, o));
+            Wt = __fadd_ru(Wt, __shfl_xor_sync(0xffffffffu, Wt, o));
+          }
+          if (lane == 0) { sm.red_s[par][warp] = S; sm.red_w[par][warp] = Wt; }
+          __syncthreads();
+          S = sm.red_s[par][0]; Wt = sm.red_w[par][0];
+          #pragma unroll
+          for (int w = 1; w < DCB_NT / 32; w++) { S = __fadd_rn(S, sm.red_s[par][w]); Wt = __fadd_ru(Wt, sm.red_w[par][w]); }
+          const float dlt = __fadd_ru(__fmul_ru(Wt, 1.02f / 16777216.0f), __fmul_ru(S, 64.0f * 1.02f / 16777216.0f));
+          const float lo = __fsub_rd(S, dlt), hi = __fadd_ru(S, dlt);
           const float fc = (float)cnt;
           const uint32_t mlo = f2u(__fdiv_rn(lo, fc)) >> 15, mhi = f2u(__fdiv_rn(hi, fc)) >> 15;
           decided = (mlo == mhi) && (f2u(hi) < 0x7F800000u);
@@ -615,25 +638,36 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
             for (int w = 1; w < DCB_NT / 32; w++) mx = fmaxf(mx, sm.red_mx[par][w]);
             float total = 0.0f;
             const float* Y = sm.X[buf];
-            for (int w = 0; w < DCB_NT / 32; w++) {
-              unsigned m = sm.walkmask[w];
-              while (m) {
-                const int t = w * 32 + (__ffs((int)m) - 1);
-                m &= m - 1u;
+            // The stop list does not depend on the running sum: the next stop's transducer is fetched while the current
+            // one is applied, so only the add (and an occasional 16-value chain) stays on the dependent path.
+            int w = 0;
+            unsigned m = sm.walkmask[0];
+            int t = -1;
+            float2 d = make_float2(0.0f, 0.0f);
+            #define DCB_NEXT_STOP(T_, D_) do {                                                             \
+                while (m == 0u && w + 1 < DCB_NT / 32) m = sm.walkmask[++w];                                \
+                if (m) { T_ = w * 32 + (__ffs((int)m) - 1); m &= m - 1u;                                    \
+                         D_ = *reinterpret_cast<const float2*>(Y + T_ * DCB_XPITCH + 16); }                 \
+                else T_ = -1;                                                                               \
+              } while (0)
+            DCB_NEXT_STOP(t, d);
+            while (t >= 0) {
+              int tn; float2 dn = make_float2(0.0f, 0.0f);
+              DCB_NEXT_STOP(tn, dn);
+              if (d.x >= 0.0f) {
+                total = __fadd_rn(total, (f2u(total) & 1u) ? d.y : d.x);      // exact
+              } else {
                 const float* yp = Y + t * DCB_XPITCH;
-                const float2 d = *reinterpret_cast<const float2*>(yp + 16);
-                if (d.x >= 0.0f) {
-                  total = __fadd_rn(total, (f2u(total) & 1u) ? d.y : d.x);    // exact
-                } else {
-                  #pragma unroll
-                  for (int q = 0; q < 4; q++) {
-                    const float4 v = *reinterpret_cast<const float4*>(yp + 4 * q);
-                    total = __fadd_rn(total, v.x); total = __fadd_rn(total, v.y);
-                    total = __fadd_rn(total, v.z); total = __fadd_rn(total, v.w);
-                  }
-                }
+                const float4 v0 = *reinterpret_cast<const float4*>(yp), v1 = *reinterpret_cast<const float4*>(yp + 4);
+                const float4 v2 = *reinterpret_cast<const float4*>(yp + 8), v3 = *reinterpret_cast<const float4*>(yp + 12);
+                total = __fadd_rn(total, v0.x); total = __fadd_rn(total, v0.y); total = __fadd_rn(total, v0.z); total = __fadd_rn(total, v0.w);
+                total = __fadd_rn(total, v1.x); total = __fadd_rn(total, v1.y); total = __fadd_rn(total, v1.z); total = __fadd_rn(total, v1.w);
+                total = __fadd_rn(total, v2.x); total = __fadd_rn(total, v2.y); total = __fadd_rn(total, v2.z); total = __fadd_rn(total, v2.w);
+                total = __fadd_rn(total, v3.x); total = __fadd_rn(total, v3.y); total = __fadd_rn(total, v3.z); total = __fadd_rn(total, v3.w);
               }
+              t = tn; d = dn;
             }
+            #undef DCB_NEXT_STOP
             const float med = __fdiv_rn(total, (float)cnt);
             const int ty = (Y[0] != Y[0]) ? 0 : type_from_max(mx);   // max starts at data[0]: NaN there defeats every '<'
             sm.med = med; sm.type = ty;
