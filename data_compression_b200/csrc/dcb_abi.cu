@@ -407,3 +407,11 @@ extern "C" int dcb_decompress_host(int ct, const uint8_t* h_stream, const uint64
   TRACE("D: output out");
   return *p_status ? DCB_EFORMAT : DCB_OK;
 }
+
+#ifdef DCB_DEBUG_COUNTERS
+extern "C" int dcb_debug_timeline(long long* host_dst) {
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpyFromSymbol(host_dst, g_dbg_ts, sizeof(g_dbg_ts)));
+  return DCB_OK;
+}
+#endif

@@ -167,13 +167,25 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 
 // Fetch tile `tile` into the staging buffer: each thread brings its own 16 consecutive floats.
-__device__ __forceinline__ void issue_tile_load(const EncArgs& a, uint32_t tile, float* slot, int tid) {
-  const uint64_t my0 = (uint64_t)tile * DCB_TILE + (uint64_t)tid * DCB_E;
-  if (my0 + DCB_E <= a.n && (a.flags & DCB_ENC_IN_ALIGNED)) {
-    const float* g = a.in + my0;
+// Tile prefetch.  A warp owns 512 consecutive floats (2 KB); it fetches them with four fully coalesced copies (lane L of copy q
+// moves the 16 bytes at offset (32 q + L) * 16), each landing in the slot of the thread that will consume those four values:
+// thread t's sixteen floats sit at Xbuf[t * DCB_XPITCH .. + 15].  (Copies in the per-thread order -- lane stride 64 B -- touch
+// 32 sectors per instruction and kept the load/store unit busy for ~0.5 us per tile.)  A thread's slot is written by four
+// different lanes of its own warp: readers need cp.async.wait_group AND __syncwarp.
+__device__ __forceinline__ void issue_tile_load(const EncArgs& a, uint32_t tile, float* Xbuf, int tid) {
+  const int lane = tid & 31;
+  const uint64_t w0 = (uint64_t)tile * DCB_TILE + (uint64_t)(tid & ~31) * DCB_E;      // first element of this warp
+  if (w0 + 32 * DCB_E <= a.n && (a.flags & DCB_ENC_IN_ALIGNED)) {                      // warp uniform
+    const float* g = a.in + w0;
+    float* sb = Xbuf + (tid & ~31) * DCB_XPITCH;
     #pragma unroll
-    for (int q = 0; q < 4; q++) cp_async16(slot + 4 * q, g + 4 * q);
-  } else {                                            // ragged last tile / unaligned input: plain loads, zero padding
+    for (int q = 0; q < 4; q++) {
+      const int u = q * 32 + lane;                      // 16-byte unit inside the warp's 2 KB
+      cp_async16(sb + (u >> 2) * DCB_XPITCH + (u & 3) * 4, g + u * 4);
+    }
+  } else {                                              // ragged last tile / unaligned input: plain loads, zero padding
+    const uint64_t my0 = (uint64_t)tile * DCB_TILE + (uint64_t)tid * DCB_E;
+    float* slot = Xbuf + tid * DCB_XPITCH;
     #pragma unroll
     for (int e = 0; e < DCB_E; e++) slot[e] = (my0 + e < a.n) ? __ldg(a.in + my0 + e) : 0.0f;
   }
@@ -283,12 +295,32 @@ __device__ __forceinline__ unsigned long long scan_apply(unsigned long long p, c
   return (x.f1 >> 31) ? (((p + b1 + 7ull) & ~7ull) + x.a + x.o) : (p + b1);
 }
 
+#ifdef DCB_DEBUG_COUNTERS
+// profiling aid (never in the shipped build): clock64 timelines of lane 0 of warps 0 and 7 of four worker blocks
+#define DBG_BLOCKS 4
+#define DBG_ITERS 40
+#define DBG_MARKS 16
+__device__ long long g_dbg_ts[DBG_BLOCKS][2][DBG_ITERS][DBG_MARKS];
+#define DBG_ADD(i, v) do {} while (0)
+#define DBG_CLK() clock64()
+#else
+#define DBG_ADD(i, v) do {} while (0)
+#define DBG_CLK() 0ll
+#endif
+// Per-tile duties with a global-memory round trip are spread over the first lanes of different warps: the warp that
+// carries one is late at the next barrier, and everybody waits for the latest warp.
+#define DCB_TKT_TID 32                                  // claims tile tickets
+#define DCB_RES_TID 64                                  // fetches the pending tile's prefix, publishes chunk offsets
+#define DCB_SCAN_PER 4                                   // status words per scanner thread and hop (1024 tiles per hop)
 struct ScanSmem {
   ScanEl wtot[DCB_NT / 32];
   uint32_t first_invalid[DCB_NT / 32];
   unsigned long long P;
 };
 
+// One hop costs an L2 round trip for the loads, a block scan and two barriers whatever its width; with 256 tiles per hop
+// the scanner topped out near 70 tiles/us and every worker ended up polling for its prefix (12-25 polls per tile in the
+// r1 profiles) -- the encoder needs 90+.  Four words per thread quadruple the width at the same hop latency.
 __device__ __noinline__ void scanner_role(const EncArgs& a, ScanSmem& ss, int tid) {
   volatile unsigned long long* status = a.status;
   const int lane = tid & 31, warp = tid >> 5;
@@ -296,15 +328,27 @@ __device__ __noinline__ void scanner_role(const EncArgs& a, ScanSmem& ss, int ti
   uint32_t q = 0u;
   unsigned long long P = 0ull;
   while (q < limit) {
-    const uint32_t j = q + (uint32_t)tid;
-    unsigned long long w = 0ull;
-    if (j < limit) w = status[j];
-    const bool valid = (w >> ST_SHIFT) != ST_INVALID;
-    const unsigned inval = __ballot_sync(0xffffffffu, !valid);
-    if (lane == 0) ss.first_invalid[warp] = inval ? (uint32_t)(__ffs(inval) - 1) : 32u;
-    ScanEl x;
-    x.f1 = ((w & ST_END_BIT) ? 0x80000000u : 0u) | (uint32_t)(w & 0x7FFFFFFFull);
-    x.a = 0u; x.o = 0u;
+    const uint32_t j0 = q + (uint32_t)tid * DCB_SCAN_PER;
+    unsigned long long w[DCB_SCAN_PER];
+    #pragma unroll
+    for (int k = 0; k < DCB_SCAN_PER; k++) w[k] = (j0 + k < limit) ? status[j0 + k] : 0ull;
+    uint32_t nv = 0u;                                   // leading valid words of this thread
+    bool open = true;
+    #pragma unroll
+    for (int k = 0; k < DCB_SCAN_PER; k++) { open = open && ((w[k] >> ST_SHIFT) != ST_INVALID); nv += open ? 1u : 0u; }
+    const unsigned inval = __ballot_sync(0xffffffffu, nv < DCB_SCAN_PER);
+    const int fl = inval ? (__ffs(inval) - 1) : 0;
+    const uint32_t nv_first = __shfl_sync(0xffffffffu, nv, fl);
+    if (lane == 0) ss.first_invalid[warp] = inval ? ((uint32_t)fl * DCB_SCAN_PER + nv_first) : 32u * DCB_SCAN_PER;
+    ScanEl xi[DCB_SCAN_PER];                            // inclusive over this thread's words
+    #pragma unroll
+    for (int k = 0; k < DCB_SCAN_PER; k++) {
+      ScanEl e;
+      e.f1 = ((w[k] & ST_END_BIT) ? 0x80000000u : 0u) | (uint32_t)(w[k] & 0x7FFFFFFFull);
+      e.a = 0u; e.o = 0u;
+      xi[k] = (k == 0) ? e : scan_combine(xi[k - 1], e);
+    }
+    ScanEl x = xi[DCB_SCAN_PER - 1];
     #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       ScanEl y;
@@ -314,21 +358,32 @@ __device__ __noinline__ void scanner_role(const EncArgs& a, ScanSmem& ss, int ti
       if (lane >= o) x = scan_combine(y, x);
     }
     if (lane == 31) ss.wtot[warp] = x;
+    ScanEl pre;                                         // exclusive prefix of this thread inside its warp
+    pre.f1 = __shfl_up_sync(0xffffffffu, x.f1, 1);
+    pre.a = __shfl_up_sync(0xffffffffu, x.a, 1);
+    pre.o = __shfl_up_sync(0xffffffffu, x.o, 1);
+    if (lane == 0) { pre.f1 = 0u; pre.a = 0u; pre.o = 0u; }
     __syncthreads();
     uint32_t m = 0u;                                    // leading valid entries of this hop
     #pragma unroll
     for (int wq = 0; wq < DCB_NT / 32; wq++) {
       const uint32_t fi = ss.first_invalid[wq];
-      if (m == 32u * wq) m += fi;
+      if (m == 32u * DCB_SCAN_PER * wq) m += fi;
     }
     if (m == 0u) { __syncthreads(); __nanosleep(100); continue; }
-    if ((uint32_t)tid < m) {
-      ScanEl pre; pre.f1 = 0u; pre.a = 0u; pre.o = 0u;
-      for (int wq = 0; wq < warp; wq++) pre = scan_combine(pre, ss.wtot[wq]);
-      const ScanEl incl = (warp > 0) ? scan_combine(pre, x) : x;
-      const unsigned long long E = scan_apply(P, incl);
-      status[j] = (ST_INCL << ST_SHIFT) | E;
-      if ((uint32_t)tid == m - 1u) ss.P = E;
+    if ((uint32_t)tid * DCB_SCAN_PER < m) {
+      ScanEl wpre; wpre.f1 = 0u; wpre.a = 0u; wpre.o = 0u;
+      for (int wq = 0; wq < warp; wq++) wpre = scan_combine(wpre, ss.wtot[wq]);
+      const ScanEl tpre = scan_combine(wpre, pre);
+      #pragma unroll
+      for (int k = 0; k < DCB_SCAN_PER; k++) {
+        const uint32_t idx = (uint32_t)tid * DCB_SCAN_PER + k;
+        if (idx < m) {
+          const unsigned long long E = scan_apply(P, scan_combine(tpre, xi[k]));
+          status[j0 + k] = (ST_INCL << ST_SHIFT) | E;
+          if (idx == m - 1u) ss.P = E;
+        }
+      }
     }
     __syncthreads();
     P = ss.P;
@@ -336,13 +391,15 @@ __device__ __noinline__ void scanner_role(const EncArgs& a, ScanSmem& ss, int ti
   }
 }
 
-// thread 0 of a worker: wait for the inclusive prefix of tile-1, publish the chunk offset of the pending tile
+// one thread of a worker (DCB_RES_TID): wait for the inclusive prefix of tile-1, publish the chunk offset of the pending tile
 __device__ __forceinline__ void resolve_pending(const EncArgs& a, EncSmem& sm, int b, unsigned long long w0) {
   volatile unsigned long long* status = a.status;
   const uint32_t tile = sm.pend_tile[b];
   unsigned long long P = 0ull;
   if (tile > 0u) {
-    while ((w0 >> ST_SHIFT) != ST_INCL) { __nanosleep(20); w0 = status[tile - 1u]; }
+    const long long dbg_t0 = DBG_CLK();
+    while ((w0 >> ST_SHIFT) != ST_INCL) { __nanosleep(20); w0 = status[tile - 1u]; DBG_ADD(2, 1); }
+    DBG_ADD(3, DBG_CLK() - dbg_t0);
     P = w0 & ST_VAL_MASK;
   }
   unsigned long long E = P + sm.pend_bits[b];
@@ -371,7 +428,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
   if (sm.role) { scanner_role(a, *reinterpret_cast<ScanSmem*>(sm.X[0]), tid); return; }
   uint32_t cur = sm.tkt[0], nxt = sm.tkt[1];
   if (cur >= a.num_tiles) return;
-  issue_tile_load(a, cur, &sm.X[0][tid * DCB_XPITCH], tid);
+  issue_tile_load(a, cur, sm.X[0], tid);
   cp_async_commit();
 
   const bool submin = (a.flags & 1u) != 0;            // DCB_F_SUBTRACT_MIN
@@ -385,24 +442,37 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
   for (;; it++) {
     const int buf = (int)(it & 1u);
     float* slot = &sm.X[buf][tid * DCB_XPITCH];
+#ifdef DCB_DEBUG_COUNTERS
+    const int dbg_blk = (int)blockIdx.x - 200;           // four blocks from the middle of the grid
+    const bool dbg_on = dbg_blk >= 0 && dbg_blk < DBG_BLOCKS && it >= 20u && it < 20u + DBG_ITERS && lane == 0 && (warp == 0 || warp == 7);
+    #define DBG_MARK(i) do { if (dbg_on) g_dbg_ts[dbg_blk][warp ? 1 : 0][it - 20u][i] = clock64(); } while (0)
+    DBG_MARK(0);
+#else
+    #define DBG_MARK(i) do {} while (0)
+#endif
     // ---- issue everything with a long latency for LATER use -------------------------------------------
-    if (nxt < a.num_tiles) issue_tile_load(a, nxt, &sm.X[buf ^ 1][tid * DCB_XPITCH], tid);
+    if (nxt < a.num_tiles) issue_tile_load(a, nxt, sm.X[buf ^ 1], tid);
     cp_async_commit();
+    DBG_MARK(1);
     uint32_t tk = 0u;
-    if (tid == 0) tk = atomicAdd(a.ticket, 1u);                         // ticket of the tile after next
+    if (tid == DCB_TKT_TID) tk = atomicAdd(a.ticket, 1u);               // ticket of the tile after next
     unsigned long long w0 = 0ull;                                       // inclusive prefix of the tile before the pending one
-    if (tid == 0 && it > 1u && sm.pend_tile[buf] > 0u) w0 = status[sm.pend_tile[buf] - 1u];   // tile packed two iterations ago
+    if (tid == DCB_RES_TID && it > 1u && sm.pend_tile[buf] > 0u) w0 = status[sm.pend_tile[buf] - 1u];   // tile packed two iterations ago
+    DBG_MARK(2);
     uint32_t* const W = sm.W[buf];                                      // staging buffer of the current tile (and of the one two iterations ago)
     if (fix_need) sm.W[buf ^ 1][fix_hw] |= sm.xchg[warp - 1];           // previous tile (ordered before its copy-out by the barriers in between)
     fix_need = false;
 
+    DBG_MARK(3);
     // ---- chunk geometry of the current tile ---------------------------------------------------------------
     const uint32_t tile = cur;
     const uint64_t base = (uint64_t)tile * DCB_TILE;
     const bool full = base + DCB_TILE <= a.n;          // block-uniform: no ragged tail in this tile
     uint32_t c = 0u, tic = 0u;                         // chunk index, tile index inside the chunk
     bool last_in_chunk = (tile == a.num_tiles - 1);
-    if (a.tiles_per_chunk) {
+    if (a.tiles_per_chunk == 1u) {
+      c = tile; last_in_chunk = true;
+    } else if (a.tiles_per_chunk) {
       c = tile / a.tiles_per_chunk;
       tic = tile - c * a.tiles_per_chunk;
       last_in_chunk = last_in_chunk || (tic == a.tiles_per_chunk - 1);
@@ -416,7 +486,10 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
     if (tid == 0 && tic > 0u && CT != CT_NP) { hr1 = __ldg(a.in + my0 - 1); hr2 = __ldg(a.in + my0 - 2); hr3 = __ldg(a.in + my0 - 3); }
 
     // ---- 1. the tile's 16 floats of this thread (landed while the previous tile was processed) ---------------
+    DBG_MARK(4);
     cp_async_wait<1>();
+    __syncwarp();                                       // the slot was filled by four lanes of this warp
+    DBG_MARK(5);
     float x[DCB_E];
     #pragma unroll
     for (int q = 0; q < 4; q++) {
@@ -453,6 +526,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
     if (tid == 0) am = fmax_nan(am, fmax_nan(fabsf(hr1), fmax_nan(fabsf(hr2), fabsf(hr3))));
     if (lane == 31) { sm.hx[par][warp][0] = x[DCB_E - 1]; sm.hx[par][warp][1] = x[DCB_E - 2]; sm.hx[par][warp][2] = x[DCB_E - 3]; }
     block_stats<CT == CT_MASK>(lmn, lmx, am, sm, par, lane, warp);
+    DBG_MARK(6);
     float mn = 0.0f;
     if (submin) mn = stats_ready ? a.cmin[c] : lmn;
     // FAST tile: every |x| (and |min|) below 2^127, so x - min is finite and >= 0; no NaN/Inf; no negative value
@@ -683,6 +757,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
       }
     }
 
+    DBG_MARK(7);
     // ---- 3. classify --------------------------------------------------------------------------------------
     uint32_t code[DCB_E];            // general path: top-aligned codes
     int len[DCB_E];
@@ -770,6 +845,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
       if (lane >= o) incl += t;
     }
     if (lane == 31) sm.warp_tot[par][warp] = incl;
+    DBG_MARK(14);
     // word-owner packing needs every thread that has bits to span a 32-bit word boundary (>= 32 bits)
     const bool fast_pack = __syncthreads_and(total >= 32u || total == 0u);
     uint32_t warp_base = 0, tile_bits = 0;
@@ -789,14 +865,18 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
       status[tile] = (ST_AGG << ST_SHIFT) | ((last_in_chunk && !single) ? ST_END_BIT : 0ull) | v;
     }
 
+    DBG_MARK(8);
     // ---- 5. finish the tile packed TWO iterations ago: its start offset (status word loaded at the top), copy-out of its staging buffer ----
     if (it > 1u) {
-      if (tid == 0) resolve_pending(a, sm, buf, w0);
+      if (tid == DCB_RES_TID) resolve_pending(a, sm, buf, w0);
       __syncthreads();
+      DBG_MARK(12);
       copy_out_tile(a, W, sm.P, sm.pend_bits[buf], sm.pend_last[buf] != 0u, tid);
+      DBG_MARK(13);
       __syncthreads();
     }
 
+    DBG_MARK(9);
     // ---- 6. pack the current tile into the staging buffer -------------------------------------------------
     uint32_t hi = 0u;                                   // on exit: the thread's unfinished last word (its tail)
     const uint32_t f0 = s & 31u;
@@ -862,11 +942,13 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
     // ---- 7. rotate the pipeline --------------------------------------------------------------------------
     if (tid == 0) {
       sm.pend_tile[buf] = tile; sm.pend_bits[buf] = tile_bits; sm.pend_c[buf] = c; sm.pend_last[buf] = last_in_chunk ? 1u : 0u;
-      sm.tkt[buf] = tk;                                  // slot of the ticket just consumed
     }
+    if (tid == DCB_TKT_TID) sm.tkt[buf] = tk;            // slot of the ticket just consumed
     par ^= 1;
     cur = nxt;
+    DBG_MARK(10);
     __syncthreads();
+    DBG_MARK(11);
     nxt = sm.tkt[buf];
     if (cur >= a.num_tiles) break;
   }
@@ -879,7 +961,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
     __syncthreads();
     for (int k = (it > 0u ? 0 : 1); k < 2; k++) {
       const int b = (k == 0) ? (lastb ^ 1) : lastb;
-      if (tid == 0) resolve_pending(a, sm, b, 0ull);
+      if (tid == DCB_RES_TID) resolve_pending(a, sm, b, 0ull);
       __syncthreads();
       copy_out_tile(a, sm.W[b], sm.P, sm.pend_bits[b], sm.pend_last[b] != 0u, tid);
       __syncthreads();
