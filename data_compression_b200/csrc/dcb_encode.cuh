@@ -148,7 +148,8 @@ struct EncSmem {
   uint32_t xchg[DCB_NT / 32];        // tail word of every warp's last lane (completes the next warp's first word)
   float hx[2][DCB_NT / 32][4];       // last three RAW values of every warp (look-back of the next warp's lane 0)
   uint32_t tkt[2];                   // prefetched tickets
-  float red_w[2][DCB_NT / 32];       // CT=7: weighted sum for the bracket of the sequential sum
+  float red_w[2][DCB_NT / 32];       // CT=7: centre and half-width of the bracket of the sequential sum
+  float red_e[2][DCB_NT / 32];
   uint32_t walkmask[DCB_NT / 32];    // exact-sum fallback: threads where the serial walk has to stop
   unsigned long long P;              // absolute bit offset of the tile being copied out
   uint32_t pend_tile[2], pend_bits[2], pend_c[2], pend_last[2];   // tiles packed in the previous two iterations (each is finished two iterations later)
@@ -589,59 +590,81 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
       if (!stats_ready) {
         const int cnt = (int)min((uint64_t)DCB_TILE, a.n - base);
         // Only the top 17 bits of medium reach the stream (mask = first 17 chars of floattostr(medium),
-        // impl/pingpong.c:202-206).  A tree sum S of the non-negative values brackets the reference's
-        // sequential float32 sum:  |S_seq - S| <= (gamma_{cnt-1} + gamma_{32}) * S  (standard forward bound,
-        // u = 2^-24).  If both ends of the bracket give the same 17 bits the mask is decided without the
-        // 4096-step dependent chain; otherwise (and for SLOW tiles) one thread runs the chain exactly.
+        // impl/pingpong.c:202-206), so the reference's SEQUENTIAL float32 sum S_seq only has to be bracketed tightly
+        // enough to pin those bits.  While the running sum stays inside one binade [2^e, 2^(e+1)) it lives on the grid
+        // q = 2^(e-23), and S -> fl(S + y) commutes with shifts of S by 2q (round-to-nearest-even only looks at the position
+        // relative to the grid and at the parity of S/q).  So a thread whose 16 values provably neither start nor end outside
+        // one binade is a 2-state transducer: S_out = S_in + d[parity(S_in)], with d[0], d[1] from two 16-step chains started
+        // at 2^e and 2^e + q -- all threads in parallel, and every d is EXACT.  Since S_seq is the sum of the 256 per-thread
+        // increments,
+        //     S_seq = sum_t d_t[0]  +-  sum_t |d_t[1] - d_t[0]|          (certain threads; the two usually coincide)
+        //                           +-  sum_t 24 ulp(hi_t)               (threads that may straddle a binade: plain sum, 16 roundings
+        //                                                                 of <= ulp(hi_t)/2 each, plus the plain sum's own)
+        // which is ~5e-6 * S for ordinary data -- 25x tighter than any a-priori bound (cnt * u * S), so that only ~0.5 % of
+        // the tiles (instead of 25 %) fall through to the exact walk below.
         bool decided = false;
         float ps = 0.0f;
+        float d0 = -1.0f, d1 = -1.0f;                      // < 0: not a transducer (the walk chains this thread's values)
+        float lo_keep = 0.0f;
+        float inc = 0.0f;
         if (!slow) {
           #pragma unroll
           for (int e = 0; e < DCB_E; e++) ps = __fadd_rn(ps, x[e]);
-        }
-        if (!slow && !(a.flags & 8u)) {                      // DCB_F_EXACT_MEDIUM skips the shortcut
-          // Bracket of the reference's sequential sum S_seq around the tree sum S (all values >= 0, u = 2^-24):
-          //   S_seq = sum(y) + sum(e_i), |e_i| <= u * s_i (round to nearest), s_i <= (1 + 1.001 i u) * P_i, P_i the exact
-          //   prefix, and sum_i P_i = sum_j y_j * (cnt - j): the error bound is u * W with W the WEIGHTED sum -- for an even
-          //   field half of the textbook cnt * u * S, which halves the number of tiles that need the exact walk.
-          //   W is accumulated rounding up; 1.02 covers the (1 + 1.001 cnt u) factor and the reduction tree's own
-          //   roundings (<= 13 adds); the tree sum itself is within 32 u of sum(y): 64 u * S with slack.
-          float pw = 0.0f;
-          {
-            float wf = (float)(cnt - tid * DCB_E);            // weights past the end multiply zero padding: their sign is irrelevant
-            #pragma unroll
-            for (int e = 0; e < DCB_E; e++) { pw = __fmaf_ru(x[e], wf, pw); wf = __fsub_rn(wf, 1.0f); }
-          }
-          float S = ps, Wt = pw;
+          inc = ps;
           #pragma unroll
-          for (int o = 16; o; o >>= 1) {
-            S = __fadd_rn(S, __shfl_xor_sync(0xffffffffu, S, o));
-            Wt = __fadd_ru(Wt, __shfl_xor_sync(0xffffffffu, Wt, o));
+          for (int o = 1; o < 32; o <<= 1) {
+            const float t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc = __fadd_rn(inc, t);
           }
-          if (lane == 0) { sm.red_s[par][warp] = S; sm.red_w[par][warp] = Wt; }
+          if (lane == 31) sm.red_s[par][warp] = inc;
           __syncthreads();
-          S = sm.red_s[par][0]; Wt = sm.red_w[par][0];
-          #pragma unroll
-          for (int w = 1; w < DCB_NT / 32; w++) { S = __fadd_rn(S, sm.red_s[par][w]); Wt = __fadd_ru(Wt, sm.red_w[par][w]); }
-          const float dlt = __fadd_ru(__fmul_ru(Wt, 1.02f / 16777216.0f), __fmul_ru(S, 64.0f * 1.02f / 16777216.0f));
-          const float lo = __fsub_rd(S, dlt), hi = __fadd_ru(S, dlt);
-          const float fc = (float)cnt;
-          const uint32_t mlo = f2u(__fdiv_rn(lo, fc)) >> 15, mhi = f2u(__fdiv_rn(hi, fc)) >> 15;
-          decided = (mlo == mhi) && (f2u(hi) < 0x7F800000u);
-          if (decided) {
-            mask17 = mlo;
-            type = type_from_max(submin ? __fsub_rn(lmx, mn) : lmx);   // max(x - min) == max(x) - min (rounding is monotone)
-            if (tid == 0) { a.cmed[c] = u2f(mask17 << 15); a.ctype[c] = type; }   // only the 17 mask bits are defined
+          float wb = 0.0f;
+          for (int w = 0; w < warp; w++) wb = __fadd_rn(wb, sm.red_s[par][w]);
+          const float pex = __fadd_rn(wb, __fsub_rn(inc, ps));             // estimate of the running sum before this thread
+          // |reference running sum - pex| <= (16 tid [its roundings] + 30 [ours]) u * sum; 96 and 1.02 leave slack
+          const float relt = (float)(16 * tid + 96) * (1.02f / 16777216.0f);
+          const float lo = __fmul_rd(pex, __fsub_rd(1.0f, relt));
+          float hi = __fmul_ru(__fadd_ru(pex, ps), __fadd_ru(1.0f, relt));
+          hi = __fmul_ru(hi, 1.00001f);                                     // the 16 round-ups inside the thread and the +q start
+          const uint32_t elo = f2u(lo) >> 23, ehi = f2u(hi) >> 23;
+          lo_keep = lo;
+          float ctr = ps, err = __fmul_ru(hi, 24.0f / 8388608.0f);          // 24 ulp(hi) <= 24 * 2^-23 * hi
+          if (elo == ehi && elo > 0u && elo < 255u) {
+            const float r0 = u2f(elo << 23), r1 = u2f((elo << 23) | 1u);
+            float c0 = r0, c1 = r1;
+            #pragma unroll
+            for (int e = 0; e < DCB_E; e++) { c0 = __fadd_rn(c0, x[e]); c1 = __fadd_rn(c1, x[e]); }
+            d0 = __fsub_rn(c0, r0); d1 = __fsub_rn(c1, r1);                 // exact: both ends lie on the grid of one binade
+            ctr = d0; err = fabsf(__fsub_rn(d1, d0));                       // exact too (a few grid steps)
+          }
+          if (!(a.flags & 8u)) {                                            // DCB_F_EXACT_MEDIUM skips the shortcut
+            #pragma unroll
+            for (int o = 16; o; o >>= 1) {
+              ctr = __fadd_rn(ctr, __shfl_xor_sync(0xffffffffu, ctr, o));
+              err = __fadd_ru(err, __shfl_xor_sync(0xffffffffu, err, o));
+            }
+            if (lane == 0) { sm.red_w[par][warp] = ctr; sm.red_e[par][warp] = err; }
+            __syncthreads();
+            float Cs = sm.red_w[par][0], Es = sm.red_e[par][0];
+            #pragma unroll
+            for (int w = 1; w < DCB_NT / 32; w++) { Cs = __fadd_rn(Cs, sm.red_w[par][w]); Es = __fadd_ru(Es, sm.red_e[par][w]); }
+            // the reduction tree of the centres (13 roundings of <= u * Cs each): 32 u * Cs with slack
+            const float dlt = __fadd_ru(__fmul_ru(Es, 1.001f), __fmul_ru(Cs, 32.0f * 1.02f / 16777216.0f));
+            const float blo = fmaxf(__fsub_rd(Cs, dlt), 0.0f), bhi = __fadd_ru(Cs, dlt);
+            const float fc = (float)cnt;
+            const uint32_t mlo = f2u(__fdiv_rn(blo, fc)) >> 15, mhi = f2u(__fdiv_rn(bhi, fc)) >> 15;
+            decided = (mlo == mhi) && (f2u(bhi) < 0x7F800000u);
+            if (decided) {
+              mask17 = mlo;
+              type = type_from_max(submin ? __fsub_rn(lmx, mn) : lmx);   // max(x - min) == max(x) - min (rounding is monotone)
+              if (tid == 0) { a.cmed[c] = u2f(mask17 << 15); a.ctype[c] = type; }   // only the 17 mask bits are defined
+            }
           }
         }
         if (!decided) {                                    // block-uniform
-          // Exact sequential sum.  While the running sum S stays inside one binade [2^e, 2^(e+1)) it lives on the grid
-          // q = 2^(e-23), and S -> fl(S + y) commutes with shifts of S by 2q (round-to-nearest-even only looks at the
-          // position relative to the grid and at the parity of S/q).  So a thread whose 16 values provably neither
-          // start nor end outside one binade is a 2-state transducer: S_out = S_in + d[parity(S_in)], and d[0], d[1]
-          // come from two 16-step chains started at 2^e and 2^e + q -- all threads in parallel.  Thread 0 then walks
-          // the 256 transducers (one exact add each) and chains the few threads that straddle a binade element by
-          // element: ~3k dependent cycles instead of 16k.  SLOW tiles (negative / NaN / Inf) keep the plain chain.
+          // Exact sequential sum: thread 0 walks the 256 transducers (one exact add each, runs of them pre-composed) and
+          // chains the few threads that straddle a binade element by element.  SLOW tiles (negative / NaN / Inf) keep the
+          // plain 4096-step chain.
           #pragma unroll
           for (int e = 0; e < DCB_E; e++) slot[e] = x[e];  // the consumed input slot doubles as the staging for thread 0
           float ymx = __uint_as_float(0xff800000u);
@@ -649,37 +672,8 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
           for (int e = 0; e < DCB_E; e++) if (e < vcnt) ymx = fmaxf(ymx, x[e]);
           #pragma unroll
           for (int o = 16; o; o >>= 1) ymx = fmaxf(ymx, __shfl_xor_sync(0xffffffffu, ymx, o));
-          float inc = ps;
-          #pragma unroll
-          for (int o = 1; o < 32; o <<= 1) {
-            const float t = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc = __fadd_rn(inc, t);
-          }
-          __syncthreads();                                 // every read of red_s / red_mx of this iteration is done
+          __syncthreads();                                 // every read of red_mx[par] by the stats reduction of this tile is done
           if (lane == 0) sm.red_mx[par][warp] = ymx;
-          if (lane == 31) sm.red_s[par][warp] = inc;
-          __syncthreads();
-          float d0 = -1.0f, d1 = -1.0f;                    // < 0: chain this thread's values from the exact running sum
-          float lo_keep = 0.0f;
-          if (!slow) {
-            float wb = 0.0f;
-            for (int w = 0; w < warp; w++) wb = __fadd_rn(wb, sm.red_s[par][w]);
-            const float pex = __fadd_rn(wb, __fsub_rn(inc, ps));           // estimate of the running sum before this thread
-            // |reference running sum - pex| <= (16 tid [its roundings] + 30 [ours]) u * sum; 96 and 1.02 leave slack
-            const float relt = (float)(16 * tid + 96) * (1.02f / 16777216.0f);
-            const float lo = __fmul_rd(pex, __fsub_rd(1.0f, relt));
-            float hi = __fmul_ru(__fadd_ru(pex, ps), __fadd_ru(1.0f, relt));
-            hi = __fmul_ru(hi, 1.00001f);                                   // the 16 round-ups inside the thread and the +q start
-            const uint32_t elo = f2u(lo) >> 23, ehi = f2u(hi) >> 23;
-            lo_keep = lo;
-            if (elo == ehi && elo > 0u && elo < 255u) {
-              const float r0 = u2f(elo << 23), r1 = u2f((elo << 23) | 1u);
-              float c0 = r0, c1 = r1;
-              #pragma unroll
-              for (int e = 0; e < DCB_E; e++) { c0 = __fadd_rn(c0, x[e]); c1 = __fadd_rn(c1, x[e]); }
-              d0 = __fsub_rn(c0, r0); d1 = __fsub_rn(c1, r1);               // exact: both ends lie on the grid of one binade
-            }
-          }
           // Runs of consecutive transducer threads in the same binade compose (associatively) into one transducer:
           // segmented warp scan.  (E then O)_p = E_p + O_{p ^ parity(E_p / q)}; every sum is exact (< 2^e, on the grid).
           {
