@@ -242,23 +242,26 @@ __device__ __forceinline__ void copy_out_tile(const EncArgs& a, const uint32_t* 
   const uint32_t sh = (uint32_t)(P & 31ull), tb = (uint32_t)(Eabs & 31ull);
   uint32_t* out32 = reinterpret_cast<uint32_t*>(a.out);
   const bool atomic_out = (a.flags & DCB_ENC_ATOMIC_OUT) != 0;
-  for (unsigned long long g = g0 + tid; g <= g1; g += DCB_NT) {
-    const uint32_t k = (uint32_t)(g - g0);
-    uint32_t v = sh ? __funnelshift_r(W[1 + k], W[k], sh) : W[1 + k];
-    const bool head = (g == g0) && sh, tail = (g == g1) && tb;
+  const uint32_t nw = (uint32_t)(g1 - g0) + 1u;            // <= DCB_TILE + 1 words
+  uint32_t* const o32 = out32 + g0;
+  #pragma unroll 4
+  for (uint32_t k = (uint32_t)tid; k < nw; k += DCB_NT) {    // independent iterations: the loads of four go out together
+    uint32_t v = __funnelshift_r(W[1 + k], W[k], sh);        // (W[k] : W[k+1]) >> sh; sh == 0 gives W[k+1]
+    const bool head = (k == 0u) && sh, tail = (k == nw - 1u) && tb;
     if (!head && !tail) {
-      out32[g] = __byte_perm(v, 0u, 0x0123);
+      o32[k] = __byte_perm(v, 0u, 0x0123);
     } else {
       const uint32_t lo_bit = head ? sh : 0u, hi_bit = tail ? tb : 32u;   // valid bits [lo_bit, hi_bit), MSB first
       uint32_t mask = 0xFFFFFFFFu >> lo_bit;
       if (hi_bit < 32u) mask &= ~(0xFFFFFFFFu >> hi_bit);
       v &= mask;
       if (atomic_out) {
-        atomicOr(&out32[g], __byte_perm(v, 0u, 0x0123));
+        atomicOr(&o32[k], __byte_perm(v, 0u, 0x0123));
       } else {
+        uint8_t* ob = reinterpret_cast<uint8_t*>(o32 + k);
         #pragma unroll
         for (uint32_t b = 0; b < 4; b++)
-          if (8u * b >= lo_bit && 8u * b + 8u <= hi_bit) a.out[g * 4ull + b] = (uint8_t)(v >> (24u - 8u * b));
+          if (8u * b >= lo_bit && 8u * b + 8u <= hi_bit) ob[b] = (uint8_t)(v >> (24u - 8u * b));
       }
     }
   }
@@ -652,7 +655,13 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
             const float dlt = __fadd_ru(__fmul_ru(Es, 1.001f), __fmul_ru(Cs, 32.0f * 1.02f / 16777216.0f));
             const float blo = fmaxf(__fsub_rd(Cs, dlt), 0.0f), bhi = __fadd_ru(Cs, dlt);
             const float fc = (float)cnt;
-            const uint32_t mlo = f2u(__fdiv_rn(blo, fc)) >> 15, mhi = f2u(__fdiv_rn(bhi, fc)) >> 15;
+            uint32_t mlo, mhi;
+            if ((cnt & (cnt - 1)) == 0) {                  // power of two (the usual 4096): an exact reciprocal, same rounding
+              const float rc = __frcp_rn(fc);
+              mlo = f2u(__fmul_rn(blo, rc)) >> 15; mhi = f2u(__fmul_rn(bhi, rc)) >> 15;
+            } else {
+              mlo = f2u(__fdiv_rn(blo, fc)) >> 15; mhi = f2u(__fdiv_rn(bhi, fc)) >> 15;
+            }
             decided = (mlo == mhi) && (f2u(bhi) < 0x7F800000u);
             if (decided) {
               mask17 = mlo;
