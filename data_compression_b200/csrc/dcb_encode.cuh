@@ -271,7 +271,7 @@ __device__ __forceinline__ void copy_out_tile(const EncArgs& a, const uint32_t* 
 // ------------------------------------------------------------------------------------------------
 // CENTRAL SCANNER.  A look-back window of 32 tiles advances the inclusive-prefix frontier by at most 32 tiles
 // per L2 round trip, which capped every earlier version at ~45 tiles/us (1.4 ms for 2^28 elements) no matter
-// how cheap the rest was (profiles/r1_v3_summary.md).  Instead the first block that starts running becomes
+// how cheap the rest was (profiles/r1_summary.md).  Instead the first block that starts running becomes
 // the scanner: it streams over the status array 256 tiles per hop, turns aggregates into inclusive prefixes
 // with a block-wide scan, and writes them back.  A worker needs exactly one word, the inclusive prefix of
 // the tile before its own, one iteration after it published its aggregate.
@@ -670,6 +670,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
             }
           }
         }
+        DBG_MARK(15);
         if (!decided) {                                    // block-uniform
           // Exact sequential sum: thread 0 walks the 256 transducers (one exact add each, runs of them pre-composed) and
           // chains the few threads that straddle a binade element by element.  SLOW tiles (negative / NaN / Inf) keep the
