@@ -675,15 +675,19 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
           // Exact sequential sum: thread 0 walks the 256 transducers (one exact add each, runs of them pre-composed) and
           // chains the few threads that straddle a binade element by element.  SLOW tiles (negative / NaN / Inf) keep the
           // plain 4096-step chain.
-          #pragma unroll
-          for (int e = 0; e < DCB_E; e++) slot[e] = x[e];  // the consumed input slot doubles as the staging for thread 0
-          float ymx = __uint_as_float(0xff800000u);
-          #pragma unroll
-          for (int e = 0; e < DCB_E; e++) if (e < vcnt) ymx = fmaxf(ymx, x[e]);
-          #pragma unroll
-          for (int o = 16; o; o >>= 1) ymx = fmaxf(ymx, __shfl_xor_sync(0xffffffffu, ymx, o));
-          __syncthreads();                                 // every read of red_mx[par] by the stats reduction of this tile is done
-          if (lane == 0) sm.red_mx[par][warp] = ymx;
+          if (d0 < 0.0f) {                                 // only threads that get chained element by element stage their values
+            #pragma unroll
+            for (int e = 0; e < DCB_E; e++) slot[e] = x[e];
+          }
+          if (slow) {                                      // the reference's max with its NaN rule; FAST tiles use max(x) - min
+            float ymx = __uint_as_float(0xff800000u);
+            #pragma unroll
+            for (int e = 0; e < DCB_E; e++) if (e < vcnt) ymx = fmaxf(ymx, x[e]);
+            #pragma unroll
+            for (int o = 16; o; o >>= 1) ymx = fmaxf(ymx, __shfl_xor_sync(0xffffffffu, ymx, o));
+            __syncthreads();                               // every read of red_mx[par] by the stats reduction of this tile is done
+            if (lane == 0) sm.red_mx[par][warp] = ymx;
+          }
           // Runs of consecutive transducer threads in the same binade compose (associatively) into one transducer:
           // segmented warp scan.  (E then O)_p = E_p + O_{p ^ parity(E_p / q)}; every sum is exact (< 2^e, on the grid).
           {
@@ -711,9 +715,12 @@ __global__ void __launch_bounds__(DCB_NT, DCB_ENC_BLOCKS_PER_SM) dcb_encode_kern
           slot[16] = d0; slot[17] = d1;
           __syncthreads();
           if (tid == 0) {
-            float mx = sm.red_mx[par][0];
-            #pragma unroll
-            for (int w = 1; w < DCB_NT / 32; w++) mx = fmaxf(mx, sm.red_mx[par][w]);
+            float mx = submin ? __fsub_rn(lmx, mn) : lmx;  // FAST tile: max(x - min) == max(x) - min (rounding is monotone)
+            if (slow) {
+              mx = sm.red_mx[par][0];
+              #pragma unroll
+              for (int w = 1; w < DCB_NT / 32; w++) mx = fmaxf(mx, sm.red_mx[par][w]);
+            }
             float total = 0.0f;
             const float* Y = sm.X[buf];
             // The stop list does not depend on the running sum: the next stop's transducer is fetched while the current
