@@ -26,6 +26,9 @@ import time
 
 import numpy as np
 
+# rank 0 prints exactly one JSON line on stdout: keep NCCL's own chatter (version banner, NCCL_DEBUG output) on stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -288,6 +291,7 @@ def run_ours(a):
             # odd threads start with the decompress of their warm-up result, so that one thread's host->device copy runs
             # against the other's device->host copy instead of both pulling in the same direction at the same time
             try:
+                torch.cuda.set_device(dev)                  # the current CUDA device is per host thread
                 for _ in range(count):
                     if t % 2 == 1 and encs[t] is not None:
                         api.decompress_host(encs[t], out=ohs[t].numpy())
