@@ -51,7 +51,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-threads", type=int, default=2, help="host threads making the blocking host-pointer calls")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--cpu-log2n", type=int, default=25, help="bounded CPU sample = 2^cpu_log2n elements")
+    ap.add_argument("--cpu-log2n", type=int, default=28, help="bounded CPU sample = 2^cpu_log2n elements (default: the whole per-GPU field, ~15 s of CPU work over 16 cores)")
     return ap.parse_args()
 
 
