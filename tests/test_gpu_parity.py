@@ -251,3 +251,44 @@ def test_error_bound_and_reference_drift(dev):
             d5 = api.decompress(c5).cpu().numpy()
             o5 = ol.o_decompress_chunked(5, ol.o_compress_chunked(5, x, 4096, eb), x.size, 4096, eb)
             assert np.abs(d5 - x).max() == np.abs(o5 - x).max()
+
+
+@pytest.mark.parametrize("ct,kind", ((7, "smooth"), (5, "noisy")))
+def test_full_size_properties(ct, kind, dev):
+    """BASELINE.json configs[1] size (2^28 elements, 65,536 chunks): what can be checked without running the CPU oracle
+    over 1 GiB.  (a) the offset table is monotone, byte aligned per chunk and ends at the stream length; (b) 96 chunks
+    sampled over the whole range -- first, last, random -- are bit-exact against the oracle run on those chunks alone
+    (chunks are independent: SURVEY 8e), stream bytes and decoded floats; (c) the CRC table computed on the GPU is a
+    checksum of every chunk's bytes: recomputed after a decode -> re-encode of the ORIGINAL input it must not move
+    (determinism: scanner/ticket order differs from launch to launch); (d) decoding never flags a malformed stream."""
+    from data_compression_b200.fields import make_field_torch
+    n, chunk, eb = 1 << 28, 4096, 0.01
+    x = make_field_torch(kind, n, dev)
+    comp = api.compress(x, ct=ct, abs_error_bound=eb, chunk_elems=chunk, crc=True)
+    K = comp.num_chunks
+    assert K == n // chunk
+    offs = comp.chunk_offsets[:K + 1]
+    assert int(offs[0].item()) == 0 and bool((offs[1:] > offs[:-1]).all().item())
+    total = comp.total_bytes()
+    assert int(offs[K].item()) == total and total <= api.lib().dcb_max_stream_bytes(n, chunk)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    out = api.decompress(comp, status=status)
+    torch.cuda.synchronize()
+    assert status.item() == 0
+    rng = np.random.default_rng(5)
+    picks = sorted(set([0, 1, K // 2, K - 2, K - 1] + [int(v) for v in rng.integers(0, K, 91)]))
+    offs_h = offs.cpu().numpy().astype(np.int64)
+    for c in picks:
+        xc = x[c * chunk:(c + 1) * chunk].cpu().numpy()
+        enc = ol.o_compress_chunked(ct, xc, chunk, eb, want_crc=True)
+        got = comp.stream[offs_h[c]:offs_h[c + 1]].cpu().numpy()
+        assert np.array_equal(got, enc["stream"]), (kind, ct, "chunk", c)
+        assert int(comp.chunk_crc[c].item()) & 0xFFFFFFFF == int(enc["chunk_crc"][0]), (kind, ct, "crc", c)
+        dec = ol.o_decompress_chunked(ct, enc, chunk, chunk, eb)
+        assert np.array_equal(out[c * chunk:(c + 1) * chunk].cpu().numpy().view(np.uint32), dec.view(np.uint32)), (kind, ct, "decoded", c)
+    crc1 = comp.chunk_crc[:K].clone()
+    tot1 = total
+    comp2 = api.compress(x, ct=ct, abs_error_bound=eb, chunk_elems=chunk, crc=True)
+    torch.cuda.synchronize()
+    assert comp2.total_bytes() == tot1 and torch.equal(comp2.chunk_crc[:K], crc1)
+    assert torch.equal(comp2.chunk_offsets[:K + 1], offs)
