@@ -26,8 +26,14 @@ import time
 
 import numpy as np
 
-# rank 0 prints exactly one JSON line on stdout: keep NCCL's own chatter (version banner, NCCL_DEBUG output) on stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# Rank 0 prints exactly ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on fd 1), so
+# fd 1 is pointed at stderr for the life of the process and the JSON line goes to a private copy of the original stdout.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -198,7 +204,7 @@ def run_reference_arm(a):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------ our arm
@@ -374,7 +380,7 @@ def run_ours(a):
     if world == 1 and not a.no_cpu:
         gbs, cores, kind, sample, _ = cpu_reference_run(a, a.cpu_log2n)
         line["cpu_baseline"] = {"value": gbs, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
