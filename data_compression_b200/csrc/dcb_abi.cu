@@ -14,6 +14,7 @@
 #include "dcb_decode.cuh"
 #include "dcb_stats.cuh"
 #include "dcb_crc.cuh"
+static int ensure_crc_tables(cudaStream_t st);
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
@@ -198,6 +199,7 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
   }
   CK(e);
   if (flags & DCB_F_CRC) {
+    { int rc_ = ensure_crc_tables(st); if (rc_) return rc_; }
     dcb_crc_kernel<<<(unsigned)((K + 3) / 4), 128, 0, st>>>(d_stream, d_offsets, K, d_ccrc);
     CK(cudaGetLastError());
   }
@@ -245,11 +247,31 @@ extern "C" int dcb_decompress(int ct, const uint8_t* d_stream, const uint64_t* d
   return DCB_OK;
 }
 
+// CRC tables live in device globals and are built by one tiny kernel the first time a device needs them
+static int ensure_crc_tables(cudaStream_t st) {
+  static std::atomic<int> ready[64];
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return DCB_EINVAL;
+  if (ready[dev].load(std::memory_order_acquire) == 0) {
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lk(mu);
+    if (ready[dev].load(std::memory_order_acquire) == 0) {
+      dcb_crc_init_kernel<<<1, 256, 0, st>>>();
+      CK(cudaGetLastError());
+      CK(cudaStreamSynchronize(st));               // other streams of this device may use the tables next
+      ready[dev].store(1, std::memory_order_release);
+    }
+  }
+  return DCB_OK;
+}
+
 extern "C" int dcb_crc32_chunks(const uint8_t* d_stream, const uint64_t* d_offsets, uint64_t K, uint32_t* d_crc,
                                 void* stream) {
   if (dcb_device_count() == 0) return DCB_ENODEVICE;
   if (K == 0) return DCB_OK;
   if (!d_stream || !d_offsets || !d_crc) return DCB_EINVAL;
+  { int rc_ = ensure_crc_tables((cudaStream_t)stream); if (rc_) return rc_; }
   dcb_crc_kernel<<<(unsigned)((K + 3) / 4), 128, 0, (cudaStream_t)stream>>>(d_stream, d_offsets, K, d_crc);
   CK(cudaGetLastError());
   return DCB_OK;
