@@ -28,7 +28,7 @@ ERRORS = {-1: "DCB_EINVAL (bad argument)", -2: "DCB_ECAPACITY (buffer too small)
 EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb", "dcb_num_chunks",
            "dcb_max_stream_bytes", "dcb_workspace_bytes", "dcb_compress", "dcb_decompress", "dcb_crc32_chunks",
            "dcb_chunk_stats", "dcb_chunk_medium", "dcb_flip_bits", "dcb_compress_host", "dcb_decompress_host",
-           "dcb_last_stream_bits"]
+           "dcb_last_stream_bits", "dcb_gather_face", "dcb_scatter_face"]
 
 _lib = None
 
@@ -64,6 +64,10 @@ def lib():
         L.dcb_chunk_stats.argtypes = [vp, u64, u64, i32, vp, vp, vp, vp]
         L.dcb_flip_bits.restype = i32
         L.dcb_flip_bits.argtypes = [vp, vp, u64, vp]
+        L.dcb_gather_face.restype = i32
+        L.dcb_gather_face.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp]
+        L.dcb_scatter_face.restype = i32
+        L.dcb_scatter_face.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, C.c_float, vp]
         L.dcb_compress_host.restype = i32
         L.dcb_compress_host.argtypes = [i32, vp, u64, u64, dbl, u32, i32, u32, vp, vp, vp, vp, vp, vp]
         L.dcb_decompress_host.restype = i32
@@ -211,6 +215,29 @@ def flip_bits(stream, bit_indices):
     idx = torch.as_tensor(bit_indices, dtype=torch.int64, device=stream.device)
     with torch.cuda.device(stream.device):
         check(lib().dcb_flip_bits(_ptr(stream), _ptr(idx), idx.numel(), _cur_stream(stream.device)), "dcb_flip_bits")
+
+
+def gather_face(p, ijk, v, imax, jmax, kmax, out=None):
+    """transform_3d_array_to_1d_array (dataCompression.c:3741-3775) on the device: p is a contiguous float32 CUDA tensor
+    [MI, MJ, MK]; returns the face i/j/k == v (ijk = 1/2/3) as a 1-D tensor in the reference's loop order."""
+    import torch
+    MI, MJ, MK = p.shape
+    n = {1: jmax * kmax, 2: imax * kmax, 3: imax * jmax}.get(ijk, 1)    # (an invalid ijk is rejected by the library)
+    if out is None:
+        out = torch.empty(n, dtype=torch.float32, device=p.device)
+    with torch.cuda.device(p.device):
+        check(lib().dcb_gather_face(_ptr(p), MI, MJ, MK, ijk, v, imax, jmax, kmax, _ptr(out), _cur_stream(p.device)),
+              "dcb_gather_face")
+    return out
+
+
+def scatter_face(p, ijk, v, imax, jmax, kmax, values, add=0.0):
+    """p[face] = values[pointer++] + add (himenoBMTxps.c:560-568): the write-back of a received halo face."""
+    import torch
+    MI, MJ, MK = p.shape
+    with torch.cuda.device(p.device):
+        check(lib().dcb_scatter_face(_ptr(p), MI, MJ, MK, ijk, v, imax, jmax, kmax, _ptr(values), float(add),
+                                     _cur_stream(p.device)), "dcb_scatter_face")
 
 
 # ---- host-pointer layer (numpy in, numpy out; H2D/D2H inside the C library) -------------------------------

@@ -14,6 +14,7 @@
 #include "dcb_decode.cuh"
 #include "dcb_stats.cuh"
 #include "dcb_crc.cuh"
+#include "dcb_face.cuh"
 static int ensure_crc_tables(cudaStream_t st);
 #include <math.h>
 #include <stdio.h>
@@ -282,6 +283,38 @@ extern "C" int dcb_flip_bits(uint8_t* d_stream, const uint64_t* d_idx, uint64_t 
   if (count == 0) return DCB_OK;
   if (!d_stream || !d_idx || ((uintptr_t)d_stream & 3)) return DCB_EINVAL;
   dcb_flip_kernel<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_stream, d_idx, count);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+
+static int face_args(int MI, int MJ, int MK, int ijk, int v, int imax, int jmax, int kmax, FaceArgs* f) {
+  if (MI <= 0 || MJ <= 0 || MK <= 0 || imax <= 0 || jmax <= 0 || kmax <= 0 || imax > MI || jmax > MJ || kmax > MK) return DCB_EINVAL;
+  f->MJ = MJ; f->MK = MK; f->ijk = ijk; f->v = v;
+  if (ijk == 1) { f->A = jmax; f->B = kmax; if (v < 0 || v >= MI) return DCB_EINVAL; }
+  else if (ijk == 2) { f->A = imax; f->B = kmax; if (v < 0 || v >= MJ) return DCB_EINVAL; }
+  else if (ijk == 3) { f->A = imax; f->B = jmax; if (v < 0 || v >= MK) return DCB_EINVAL; }
+  else return DCB_EINVAL;                      // the reference leaves A, B uninitialised here
+  return DCB_OK;
+}
+
+extern "C" int dcb_gather_face(const float* d_p, int MI, int MJ, int MK, int ijk, int v, int imax, int jmax, int kmax,
+                               float* d_out, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  FaceArgs f;
+  if (!d_p || !d_out || face_args(MI, MJ, MK, ijk, v, imax, jmax, kmax, &f)) return DCB_EINVAL;
+  const size_t n = (size_t)f.A * f.B;
+  dcb_gather_face_kernel<<<(unsigned)((n + 255) / 256 < 4096 ? (n + 255) / 256 : 4096), 256, 0, (cudaStream_t)stream>>>(d_p, f, d_out);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+
+extern "C" int dcb_scatter_face(float* d_p, int MI, int MJ, int MK, int ijk, int v, int imax, int jmax, int kmax,
+                                const float* d_in, float add, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  FaceArgs f;
+  if (!d_p || !d_in || face_args(MI, MJ, MK, ijk, v, imax, jmax, kmax, &f)) return DCB_EINVAL;
+  const size_t n = (size_t)f.A * f.B;
+  dcb_scatter_face_kernel<<<(unsigned)((n + 255) / 256 < 4096 ? (n + 255) / 256 : 4096), 256, 0, (cudaStream_t)stream>>>(d_p, f, d_in, add);
   CK(cudaGetLastError());
   return DCB_OK;
 }

@@ -94,6 +94,15 @@ int dcb_chunk_medium(const float* d_in, uint64_t n, float* d_medium, int32_t* d_
 /* bit_flip (dataCompression.c:5858) test hook: flips bit (7 - bit_index%8) of byte bit_index/8 for each index */
 int dcb_flip_bits(uint8_t* d_stream, const uint64_t* d_bit_indices, uint64_t count, void* cuda_stream);
 
+/* Himeno halo faces, device resident.  dcb_gather_face replaces transform_3d_array_to_1d_array
+ * (impl/dataCompression.c:3741-3775; p is float[MI][MJ][MK], ijk = 1/2/3 fixes i/j/k = v, the face has jmax*kmax /
+ * imax*kmax / imax*jmax elements in the reference's loop order); dcb_scatter_face replaces the loops that write a
+ * decompressed face back, p[face] = d_in[pointer++] + add (impl/himenoBMTxps.c:560-568, :640-648). */
+int dcb_gather_face(const float* d_p, int MI, int MJ, int MK, int ijk, int v, int imax, int jmax, int kmax,
+                    float* d_out, void* cuda_stream);
+int dcb_scatter_face(float* d_p, int MI, int MJ, int MK, int ijk, int v, int imax, int jmax, int kmax,
+                     const float* d_in, float add, void* cuda_stream);
+
 /* ---- host-pointer convenience (what the legacy symbols and the end-to-end bench call) ----------------
  * Pinned staging + H2D + kernels + D2H inside.  h_stream needs dcb_max_stream_bytes(); tables need K(+1). */
 int dcb_compress_host(int ct, const float* h_in, uint64_t n, uint64_t chunk_elems, double abs_error_bound,

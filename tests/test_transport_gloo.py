@@ -144,3 +144,99 @@ def test_frames_over_gloo_world2():
     for p in procs:
         p.join(timeout=60)
     assert all(r[1] == "ok" for r in res), res
+
+
+# ---- Himeno halo exchange protocol (data_compression_b200/halo.py) with the oracle as the codec -------------------------
+def _np_face(p, ijk, v, imax, jmax, kmax):
+    if ijk == 1:
+        return p[v, :jmax, :kmax].reshape(-1).copy()
+    if ijk == 2:
+        return p[:imax, v, :kmax].reshape(-1).copy()
+    return p[:imax, :jmax, v].reshape(-1).copy()
+
+
+def _halo_field(rank, MI, MJ, MK):
+    i, j, k = np.meshgrid(np.arange(MI), np.arange(MJ), np.arange(MK), indexing="ij")
+    return (0.01 * i + 0.02 * j + 0.03 * k + 10.0 * rank + 0.001 * np.sin(i * j + k)).astype(np.float32)
+
+
+def _halo_worker(rank, world, port, q):
+    import torch.distributed as dist
+    from data_compression_b200 import halo
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        MI, MJ, MK = 10, 12, 14
+        imax, jmax, kmax = 9, 11, 13
+        eb = 0.001
+
+        def compress_fn(p, ijk, v, im, jm, km, ct, e):
+            face = _np_face(p.numpy(), ijk, v, im, jm, km)
+            enc = ol.o_compress_chunked(ct, face, face.size, e, want_crc=True)
+            pad = np.zeros(((enc["stream"].size + 31) // 16) * 16, np.uint8)
+            pad[:enc["stream"].size] = enc["stream"]
+            return HostCompressed(ct, face.size, 0, e, 1, 0, 0, torch.from_numpy(pad), torch.from_numpy(enc["offsets"].astype(np.int64)),
+                                  torch.from_numpy(enc["chunk_min"]), torch.from_numpy(enc["chunk_medium"]),
+                                  torch.from_numpy(enc["chunk_type"]), torch.from_numpy(enc["chunk_crc"].view(np.int32).copy()))
+
+        def write_fn(p, ijk, v, im, jm, km, comp):
+            total = int(comp.chunk_offsets[-1])
+            enc = dict(stream=comp.stream[:total].numpy(), offsets=comp.chunk_offsets.numpy().astype(np.uint64),
+                       chunk_min=comp.chunk_min.numpy(), chunk_medium=comp.chunk_medium.numpy(), chunk_type=comp.chunk_type.numpy())
+            dec = ol.o_decompress_chunked(comp.ct, enc, comp.n, comp.n, comp.abs_error_bound)
+            a = p.numpy()
+            if ijk == 1:
+                a[v, :jm, :km] = dec.reshape(jm, km)
+            elif ijk == 2:
+                a[:im, v, :km] = dec.reshape(im, km)
+            else:
+                a[:im, :jm, v] = dec.reshape(im, jm)
+
+        def expect(src_rank, ijk, v):
+            face = _np_face(_halo_field(src_rank, MI, MJ, MK), ijk, v, imax, jmax, kmax)
+            enc = ol.o_compress_chunked(5, face, face.size, eb)
+            return ol.o_decompress_chunked(5, enc, face.size, face.size, eb)
+
+        peer = 1 - rank
+        # (a) open chain along k: rank 0 has only a hi neighbour, rank 1 only a lo neighbour
+        p = torch.from_numpy(_halo_field(rank, MI, MJ, MK))
+        before = p.numpy().copy()
+        sent = halo.exchange_axis(p, 3, imax, jmax, kmax, None if rank == 0 else 0, 1 if rank == 0 else None, ct=5, eb=eb,
+                                  compressed_cls=HostCompressed, compress_fn=compress_fn, write_fn=write_fn)
+        assert sent > 0
+        a = p.numpy()
+        if rank == 0:
+            assert np.array_equal(_np_face(a, 3, kmax - 1, imax, jmax, kmax).view(np.uint32), expect(1, 3, 1).view(np.uint32))
+            assert np.array_equal(a[:, :, 0], before[:, :, 0])                      # no lo neighbour: plane 0 untouched
+        else:
+            assert np.array_equal(_np_face(a, 3, 0, imax, jmax, kmax).view(np.uint32), expect(0, 3, kmax - 2).view(np.uint32))
+            assert np.array_equal(a[:, :, kmax - 1], before[:, :, kmax - 1])
+        # (b) periodic along i with two ranks: both neighbours are the same rank
+        p = torch.from_numpy(_halo_field(rank, MI, MJ, MK))
+        halo.exchange_axis(p, 1, imax, jmax, kmax, peer, peer, ct=5, eb=eb, compressed_cls=HostCompressed,
+                           compress_fn=compress_fn, write_fn=write_fn)
+        a = p.numpy()
+        assert np.array_equal(_np_face(a, 1, imax - 1, imax, jmax, kmax).view(np.uint32), expect(peer, 1, 1).view(np.uint32))
+        assert np.array_equal(_np_face(a, 1, 0, imax, jmax, kmax).view(np.uint32), expect(peer, 1, imax - 2).view(np.uint32))
+        q.put((rank, "ok"))
+    except Exception as e:  # pragma: no cover
+        import traceback
+        q.put((rank, "FAIL: %s\n%s" % (e, traceback.format_exc())))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_halo_exchange_over_gloo_world2():
+    import torch.multiprocessing as mp
+    ol.build_oracle()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_halo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(r[1] == "ok" for r in res), res
