@@ -28,7 +28,8 @@ ERRORS = {-1: "DCB_EINVAL (bad argument)", -2: "DCB_ECAPACITY (buffer too small)
 EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb", "dcb_num_chunks",
            "dcb_max_stream_bytes", "dcb_workspace_bytes", "dcb_compress", "dcb_decompress", "dcb_crc32_chunks",
            "dcb_chunk_stats", "dcb_chunk_medium", "dcb_flip_bits", "dcb_compress_host", "dcb_decompress_host",
-           "dcb_last_stream_bits", "dcb_gather_face", "dcb_scatter_face"]
+           "dcb_last_stream_bits", "dcb_gather_face", "dcb_scatter_face", "dcb_himeno_jacobi",
+           "dcb_himeno_copy_interior"]
 
 _lib = None
 
@@ -66,6 +67,10 @@ def lib():
         L.dcb_flip_bits.argtypes = [vp, vp, u64, vp]
         L.dcb_gather_face.restype = i32
         L.dcb_gather_face.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp]
+        L.dcb_himeno_jacobi.restype = i32
+        L.dcb_himeno_jacobi.argtypes = [vp] * 7 + [i32] * 6 + [C.c_float, vp, vp]
+        L.dcb_himeno_copy_interior.restype = i32
+        L.dcb_himeno_copy_interior.argtypes = [vp, vp] + [i32] * 6 + [vp]
         L.dcb_scatter_face.restype = i32
         L.dcb_scatter_face.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, C.c_float, vp]
         L.dcb_compress_host.restype = i32
@@ -238,6 +243,21 @@ def scatter_face(p, ijk, v, imax, jmax, kmax, values, add=0.0):
     with torch.cuda.device(p.device):
         check(lib().dcb_scatter_face(_ptr(p), MI, MJ, MK, ijk, v, imax, jmax, kmax, _ptr(values), float(add),
                                      _cur_stream(p.device)), "dcb_scatter_face")
+
+
+def himeno_jacobi(p, a, b, c, bnd, wrk1, wrk2, imax, jmax, kmax, omega=0.8, gosa=None):
+    """One Jacobi sweep of impl/himenoBMTxps.c:247-284 (without the halo exchange): wrk2 on the interior, then p = wrk2.
+    Returns the device scalar (float64) sum ss^2 of this rank."""
+    import torch
+    MI, MJ, MK = p.shape
+    if gosa is None:
+        gosa = torch.zeros(1, dtype=torch.float64, device=p.device)
+    with torch.cuda.device(p.device):
+        st = _cur_stream(p.device)
+        check(lib().dcb_himeno_jacobi(_ptr(p), _ptr(a), _ptr(b), _ptr(c), _ptr(bnd), _ptr(wrk1), _ptr(wrk2), MI, MJ, MK,
+                                      imax, jmax, kmax, float(omega), _ptr(gosa), st), "dcb_himeno_jacobi")
+        check(lib().dcb_himeno_copy_interior(_ptr(p), _ptr(wrk2), MI, MJ, MK, imax, jmax, kmax, st), "dcb_himeno_copy_interior")
+    return gosa
 
 
 # ---- host-pointer layer (numpy in, numpy out; H2D/D2H inside the C library) -------------------------------

@@ -319,6 +319,35 @@ extern "C" int dcb_scatter_face(float* d_p, int MI, int MJ, int MK, int ijk, int
   return DCB_OK;
 }
 
+extern "C" int dcb_himeno_jacobi(const float* d_p, const float* d_a, const float* d_b, const float* d_c, const float* d_bnd,
+                                 const float* d_wrk1, float* d_wrk2, int MI, int MJ, int MK, int imax, int jmax, int kmax,
+                                 float omega, double* d_gosa, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (!d_p || !d_a || !d_b || !d_c || !d_bnd || !d_wrk1 || !d_wrk2 || !d_gosa) return DCB_EINVAL;
+  if (imax < 3 || jmax < 3 || kmax < 3 || imax > MI || jmax > MJ || kmax > MK) return DCB_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  JacobiArgs q;
+  q.p = d_p; q.a = d_a; q.b = d_b; q.c = d_c; q.bnd = d_bnd; q.wrk1 = d_wrk1; q.wrk2 = d_wrk2;
+  q.MI = MI; q.MJ = MJ; q.MK = MK; q.imax = imax; q.jmax = jmax; q.kmax = kmax; q.omega = omega; q.gosa = d_gosa;
+  CK(cudaMemsetAsync(d_gosa, 0, sizeof(double), st));
+  const size_t total = (size_t)(imax - 2) * (jmax - 2) * (kmax - 2);
+  const unsigned grid = (unsigned)((total + 255) / 256 < (size_t)num_sms() * 16 ? (total + 255) / 256 : (size_t)num_sms() * 16);
+  dcb_himeno_jacobi_kernel<<<grid, 256, 0, st>>>(q);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+
+extern "C" int dcb_himeno_copy_interior(float* d_p, const float* d_wrk2, int MI, int MJ, int MK, int imax, int jmax, int kmax,
+                                        void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (!d_p || !d_wrk2 || imax < 3 || jmax < 3 || kmax < 3 || imax > MI || jmax > MJ || kmax > MK) return DCB_EINVAL;
+  const size_t total = (size_t)(imax - 2) * (jmax - 2) * (kmax - 2);
+  const unsigned grid = (unsigned)((total + 255) / 256 < (size_t)num_sms() * 16 ? (total + 255) / 256 : (size_t)num_sms() * 16);
+  dcb_himeno_copy_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_p, d_wrk2, MJ, MK, imax, jmax, kmax);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+
 // ---- host-pointer layer: cached device buffers (grow only), one stream ---------------------------------------
 struct HostCtx {
   cudaStream_t st = nullptr;

@@ -72,3 +72,31 @@ def exchange_axis(p, ijk, imax, jmax, kmax, lo_peer, hi_peer, ct=5, eb=0.01, com
     if in_lo_t is not None:
         write_fn(p, ijk, 0, imax, jmax, kmax, tr.unpack_frame(tr.Frame(in_lo_t, in_lo_s[0]), cls))
     return (out_lo.stream.numel() if out_lo is not None else 0) + (out_hi.stream.numel() if out_hi is not None else 0)
+
+
+def exchange_axis_raw(p, ijk, imax, jmax, kmax, lo_peer, hi_peer):
+    """CT=0: the uncompressed faces (the reference's MPI vector types, impl/himenoBMTxps.c sendp1/2/3 default branch) -- one
+    batched round of float32 faces.  Returns the bytes sent."""
+    import torch
+    import torch.distributed as dist
+    ext = {1: imax, 2: jmax, 3: kmax}[ijk]
+    n = {1: jmax * kmax, 2: imax * kmax, 3: imax * jmax}[ijk]
+    dev = p.device
+    out_lo = api.gather_face(p, ijk, 1, imax, jmax, kmax) if lo_peer is not None else None
+    out_hi = api.gather_face(p, ijk, ext - 2, imax, jmax, kmax) if hi_peer is not None else None
+    in_hi = torch.empty(n, dtype=torch.float32, device=dev) if hi_peer is not None else None
+    in_lo = torch.empty(n, dtype=torch.float32, device=dev) if lo_peer is not None else None
+    ops = []
+    if out_lo is not None: ops.append(dist.P2POp(dist.isend, out_lo, lo_peer))
+    if out_hi is not None: ops.append(dist.P2POp(dist.isend, out_hi, hi_peer))
+    if in_hi is not None: ops.append(dist.P2POp(dist.irecv, in_hi, hi_peer))
+    if in_lo is not None: ops.append(dist.P2POp(dist.irecv, in_lo, lo_peer))
+    if not ops:
+        return 0
+    for w in dist.batch_isend_irecv(ops):
+        w.wait()
+    if in_hi is not None:
+        api.scatter_face(p, ijk, ext - 1, imax, jmax, kmax, in_hi, 0.0)
+    if in_lo is not None:
+        api.scatter_face(p, ijk, 0, imax, jmax, kmax, in_lo, 0.0)
+    return 4 * n * ((out_lo is not None) + (out_hi is not None))

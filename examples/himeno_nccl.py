@@ -1,0 +1,148 @@
+#!/usr/bin/env python
+"""Himeno benchmark with compressed halo faces, device resident (impl/himenoBMTxps.c: initmt :203-246, jacobi :247-299,
+sendp3 :580-650).  Ranks form an open chain along k (the driver's ndx=ndy=1, ndz=world); each rank holds its block on its
+GPU, runs the Jacobi sweep kernel, exchanges the two k-faces (raw for --ct 0, compressed for 5/6/7) and all-reduces gosa.
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29522 \
+      examples/himeno_nccl.py [--ct 5] [--size 129] [--eb 1e-4] [--nn 50] [--check]
+
+--check (ct 0): the chained blocks must reproduce a single-domain float32 numpy sweep bit for bit;
+        (ct>0): the pressure must stay within nn * eb of the uncompressed run (every exchange adds at most eb per face value).
+
+Note on --eb: a k-face of this field spans only ~3e-5 after the min subtraction.  With eb >= 1e-5 the codec sends every value
+as the zero code (the face becomes its minimum); with eb = 1e-6 the REFERENCE's CT=5/7 stream decodes to non-finite values on
+these faces after ~30 sweeps at 257^3 (reproduced with the compiled reference in oracle/_ref; this library is bit-identical
+to it, so the run diverges here exactly as the reference's would).  CT=6 stays finite at every eb.
+"""
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from data_compression_b200 import api, halo          # noqa: E402
+
+
+class Block:
+    """One rank's arrays as initmt() sets them; k is the partitioned axis (global extent kg, my planes [k0, k0+kmax))."""
+
+    def __init__(self, m, kmax, k0, kg, dev):
+        f = torch.float32
+        self.imax = self.jmax = m
+        self.kmax = kmax
+        sh = (m, m, kmax)
+        self.a = torch.ones((4,) + sh, dtype=f, device=dev)
+        self.a[3] = float(np.float32(1.0 / 6.0))
+        self.b = torch.zeros((3,) + sh, dtype=f, device=dev)
+        self.c = torch.ones((3,) + sh, dtype=f, device=dev)
+        self.bnd = torch.ones(sh, dtype=f, device=dev)
+        self.wrk1 = torch.zeros(sh, dtype=f, device=dev)
+        self.wrk2 = torch.zeros(sh, dtype=f, device=dev)
+        k = np.arange(k0, k0 + kmax, dtype=np.float32)                  # (float)(k*k) / (float)((mz-1)*(mz-1)): a true division
+        pk = (k * k) / np.float32((kg - 1) * (kg - 1))
+        self.p = torch.from_numpy(pk).to(dev).expand(sh).contiguous()
+
+    def sweep(self, omega=0.8):
+        return api.himeno_jacobi(self.p, self.a, self.b, self.c, self.bnd, self.wrk1, self.wrk2,
+                                 self.imax, self.jmax, self.kmax, omega)
+
+
+def run(a, ct, rank, world, dev):
+    m = a.size
+    inner = m - 2                                       # interior planes per rank
+    kg = world * inner + 2
+    blk = Block(m, m, rank * inner, kg, dev)
+    lo = rank - 1 if rank > 0 else None
+    hi = rank + 1 if rank < world - 1 else None
+    sent = 0
+    gosa = torch.zeros(1, dtype=torch.float64, device=dev)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); dist.barrier()
+    ev0.record()
+    for _ in range(a.nn):
+        g = blk.sweep()
+        if ct == 0:
+            sent += halo.exchange_axis_raw(blk.p, 3, m, m, m, lo, hi)
+        else:
+            sent += halo.exchange_axis(blk.p, 3, m, m, m, lo, hi, ct=ct, eb=a.eb)
+        gosa.copy_(g)
+        dist.all_reduce(gosa)
+    ev1.record()
+    torch.cuda.synchronize(); dist.barrier()
+    ms = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return blk, float(gosa.item()), sent, float(ms.item())
+
+
+def numpy_single_domain(m, kg, nn, omega=0.8):
+    f = np.float32
+    k = np.arange(kg, dtype=f)
+    p = np.broadcast_to((k * k) / f((kg - 1) * (kg - 1)), (m, m, kg)).copy()
+    a3 = f(1.0 / 6.0)
+    for _ in range(nn):
+        def sh(di, dj, dk):
+            return p[1 + di:m - 1 + di, 1 + dj:m - 1 + dj, 1 + dk:kg - 1 + dk]
+        s0 = sh(1, 0, 0) * f(1)
+        s0 = s0 + sh(0, 1, 0)
+        s0 = s0 + sh(0, 0, 1)
+        for t in (((1, 1, 0), (1, -1, 0), (-1, 1, 0), (-1, -1, 0)), ((0, 1, 1), (0, -1, 1), (0, 1, -1), (0, -1, -1)),
+                  ((1, 0, 1), (-1, 0, 1), (1, 0, -1), (-1, 0, -1))):
+            s0 = s0 + f(0) * (((sh(*t[0]) - sh(*t[1])) - sh(*t[2])) + sh(*t[3]))
+        s0 = s0 + sh(-1, 0, 0)
+        s0 = s0 + sh(0, -1, 0)
+        s0 = s0 + sh(0, 0, -1)
+        s0 = s0 + f(0)
+        ss = (s0 * a3 - sh(0, 0, 0)) * f(1)
+        w = sh(0, 0, 0) + f(omega) * ss
+        p[1:m - 1, 1:m - 1, 1:kg - 1] = w
+    return p
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--ct", type=int, default=5)
+    ap.add_argument("--size", type=int, default=129)
+    ap.add_argument("--eb", type=float, default=1e-4)
+    ap.add_argument("--nn", type=int, default=50)
+    ap.add_argument("--check", action="store_true")
+    a = ap.parse_args()
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    m = a.size
+    run(argparse.Namespace(size=m, eb=a.eb, nn=2), a.ct, rank, world, dev)             # warm-up (NCCL channels, allocator)
+    blk, gosa, sent, ms = run(a, a.ct, rank, world, dev)
+    ok, note = True, ""
+    if a.check:
+        inner = m - 2
+        kg = world * inner + 2
+        if a.ct == 0:
+            want = numpy_single_domain(m, kg, a.nn)[:, :, rank * inner:rank * inner + m]
+            ok = np.array_equal(blk.p.cpu().numpy().view(np.uint32), want.view(np.uint32))
+            note = "  single-domain numpy check=%s" % ("OK" if ok else "MISMATCH")
+        else:
+            ref, _, _, _ = run(a, 0, rank, world, dev)
+            dmax = float((blk.p - ref.p).abs().max().item())
+            ok = dmax <= a.nn * a.eb
+            note = "  max |p - p_uncompressed| = %.3g (bound nn*eb = %.3g) %s" % (dmax, a.nn * a.eb, "OK" if ok else "EXCEEDED")
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        flop = 34.0 * (m - 2) * (m - 2) * (world * (m - 2)) * a.nn          # the driver's count: 34 flop per interior point
+        faces = (world > 1) * 1
+        raw = a.nn * faces * m * m * 4
+        print("himeno ct=%d %dx%dx%d on %d ranks, nn=%d: gosa=%.6e  %.3f ms/iter  %.1f GFLOPS  halo bytes rank0 %d (raw %d, ratio %.2f)%s"
+              % (a.ct, m, m, world * (m - 2) + 2, world, a.nn, gosa, ms / a.nn, flop / ms / 1e6, sent, raw, raw / max(sent, 1), note),
+              flush=True)
+    dist.destroy_process_group()
+    if not flag.item():
+        raise SystemExit(1)
+
+
+if __name__ == "__main__":
+    main()

@@ -103,6 +103,16 @@ int dcb_gather_face(const float* d_p, int MI, int MJ, int MK, int ijk, int v, in
 int dcb_scatter_face(float* d_p, int MI, int MJ, int MK, int ijk, int v, int imax, int jmax, int kmax,
                      const float* d_in, float add, void* cuda_stream);
 
+/* Himeno Jacobi sweep on the device (impl/himenoBMTxps.c:247-284): arrays as in the driver -- p, bnd, wrk1, wrk2 are
+ * float[MI][MJ][MK], a is float[4][MI][MJ][MK], b and c float[3][MI][MJ][MK].  dcb_himeno_jacobi writes wrk2 on the interior
+ * (bit exact: every operation rounded in the C expression's order) and *d_gosa = sum ss^2 (double); dcb_himeno_copy_interior
+ * is the p = wrk2 loop (:279-282).  The halo exchange between the two is halo.exchange_axis / dcb_gather_face etc. */
+int dcb_himeno_jacobi(const float* d_p, const float* d_a, const float* d_b, const float* d_c, const float* d_bnd,
+                      const float* d_wrk1, float* d_wrk2, int MI, int MJ, int MK, int imax, int jmax, int kmax,
+                      float omega, double* d_gosa, void* cuda_stream);
+int dcb_himeno_copy_interior(float* d_p, const float* d_wrk2, int MI, int MJ, int MK, int imax, int jmax, int kmax,
+                             void* cuda_stream);
+
 /* ---- host-pointer convenience (what the legacy symbols and the end-to-end bench call) ----------------
  * Pinned staging + H2D + kernels + D2H inside.  h_stream needs dcb_max_stream_bytes(); tables need K(+1). */
 int dcb_compress_host(int ct, const float* h_in, uint64_t n, uint64_t chunk_elems, double abs_error_bound,
