@@ -53,6 +53,24 @@ int dco_decompress_chunked(int ct, const uint8_t* s, const uint64_t* offsets, si
                            double eb, int add_min, const float* chunk_min, int fixed_type,
                            uint32_t fixed_mask17, const float* chunk_medium, const int32_t* chunk_type,
                            float* out);
+
+/* ---- float64 variants (dc_oracle_f64.c).  Same contracts with double data, 8*n+16 byte worst case,
+ * and the CT=7 mask as the first 1+11+8 = 20 bits of the chunk mean (impl/k-means.c:527-530). ---- */
+double dco_min_subtract_f64(const double* x, size_t n, double* y);           /* toSmallDataset_double :3522-3541 */
+double dco_med_f64(const double* x, size_t n, int* type);                    /* med_dataset_double :3564-3591 */
+uint32_t dco_mask20(double medium);
+size_t dco_compress_f64(int ct, const double* x, size_t n, double eb, int type, uint32_t mask20,
+                        uint8_t* out, int* pos_out);
+int dco_decompress_f64(int ct, const uint8_t* s, size_t bytes, size_t n, double eb, int type, uint32_t mask20,
+                       double* out);
+size_t dco_compress_chunked_f64(int ct, const double* x, size_t n, size_t chunk_elems, double eb, int subtract_min,
+                                int fixed_type, uint32_t fixed_mask20,
+                                uint8_t* out, uint64_t* offsets, double* chunk_min, double* chunk_medium,
+                                int32_t* chunk_type, uint32_t* chunk_crc);
+int dco_decompress_chunked_f64(int ct, const uint8_t* s, const uint64_t* offsets, size_t n, size_t chunk_elems,
+                               double eb, int add_min, const double* chunk_min, int fixed_type,
+                               uint32_t fixed_mask20, const uint32_t* chunk_mask20, const int32_t* chunk_type,
+                               double* out);
 #ifdef __cplusplus
 }
 #endif

@@ -29,8 +29,8 @@ def eb_str(eb):
 
 
 def build_oracle():
-    src = os.path.join(ORACLE_DIR, "dc_oracle.c")
-    if (not os.path.exists(ORACLE_SO)) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(ORACLE_DIR, f) for f in ("dc_oracle.c", "dc_oracle_f64.c", "dc_oracle.h")]
+    if (not os.path.exists(ORACLE_SO)) or os.path.getmtime(ORACLE_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", ORACLE_DIR, "_build/libdc_oracle.so"], stdout=subprocess.DEVNULL)
     return ORACLE_SO
 
@@ -66,6 +66,20 @@ def oracle():
         lib.dco_decompress_chunked.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
                                                C.c_double, C.c_int, C.c_void_p, C.c_int, C.c_uint32,
                                                C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.dco_min_subtract_f64.restype = C.c_double
+        lib.dco_min_subtract_f64.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+        lib.dco_med_f64.restype = C.c_double
+        lib.dco_med_f64.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_int)]
+        lib.dco_mask20.restype = C.c_uint32
+        lib.dco_mask20.argtypes = [C.c_double]
+        lib.dco_compress_f64.restype = C.c_size_t
+        lib.dco_compress_f64.argtypes = lib.dco_compress.argtypes
+        lib.dco_decompress_f64.restype = C.c_int
+        lib.dco_decompress_f64.argtypes = lib.dco_decompress.argtypes
+        lib.dco_compress_chunked_f64.restype = C.c_size_t
+        lib.dco_compress_chunked_f64.argtypes = lib.dco_compress_chunked.argtypes
+        lib.dco_decompress_chunked_f64.restype = C.c_int
+        lib.dco_decompress_chunked_f64.argtypes = lib.dco_decompress_chunked.argtypes
         _oracle = lib
     return _oracle
 
@@ -303,3 +317,163 @@ def ref_mask_decode_defined(type_, mask17, eb):
         return False
     k0 = max(m - 8, 0)
     return (type_ + 2 + k0 != 9) and (type_ + 2 + m != 9)
+
+
+# ------------------------------------------------------------------ float64 variants
+_f64p = C.POINTER(C.c_double)
+
+
+def _f64(x):
+    return np.ascontiguousarray(x, dtype=np.float64)
+
+
+def mask20_of(medium):
+    return int(np.array([medium], dtype=np.float64).view(np.uint64)[0] >> np.uint64(44))
+
+
+def o_min_subtract_f64(x):
+    x = _f64(x)
+    y = np.empty_like(x)
+    mn = oracle().dco_min_subtract_f64(_ptr(x), x.size, _ptr(y))
+    return np.float64(mn), y
+
+
+def o_med_f64(x, type0=0):
+    x = _f64(x)
+    t = C.c_int(type0)
+    med = oracle().dco_med_f64(_ptr(x), x.size, C.byref(t))
+    return np.float64(med), t.value
+
+
+def o_compress_f64(ct, x, eb, type_=0, mask20=0):
+    x = _f64(x)
+    out = np.zeros(8 * x.size + 16, dtype=np.uint8)
+    pos = C.c_int(0)
+    nb = oracle().dco_compress_f64(ct, _ptr(x), x.size, eb, type_, mask20, _ptr(out), C.byref(pos))
+    return out[:nb].copy(), pos.value
+
+
+def o_decompress_f64(ct, stream, n, eb, type_=0, mask20=0):
+    s = np.ascontiguousarray(stream, dtype=np.uint8)
+    out = np.empty(n, dtype=np.float64)
+    rc = oracle().dco_decompress_f64(ct, _ptr(s), s.size, n, eb, type_, mask20, _ptr(out))
+    if rc:
+        raise ValueError("oracle: malformed stream (rc=%d)" % rc)
+    return out
+
+
+def o_compress_chunked_f64(ct, x, chunk, eb, subtract_min=True, fixed_type=-1, fixed_mask20=0, want_crc=False):
+    """-> dict(stream, offsets, chunk_min, chunk_medium, chunk_mask20, chunk_type, chunk_crc)"""
+    x = _f64(x)
+    n = x.size
+    K = (n + chunk - 1) // chunk if n else 0
+    out = np.zeros(8 * n + 16 * max(K, 1), dtype=np.uint8)
+    offs = np.zeros(K + 1, dtype=np.uint64)
+    cmin = np.zeros(K, dtype=np.float64)
+    cmed = np.zeros(K, dtype=np.float64)
+    ctype = np.zeros(K, dtype=np.int32)
+    ccrc = np.zeros(K, dtype=np.uint32) if want_crc else None
+    tot = oracle().dco_compress_chunked_f64(ct, _ptr(x), n, chunk, eb, int(subtract_min), fixed_type, fixed_mask20,
+                                            _ptr(out), _ptr(offs), _ptr(cmin), _ptr(cmed), _ptr(ctype), _ptr(ccrc))
+    return dict(stream=out[:tot].copy(), offsets=offs, chunk_min=cmin, chunk_medium=cmed,
+                chunk_mask20=(cmed.view(np.uint64) >> np.uint64(44)).astype(np.uint32), chunk_type=ctype, chunk_crc=ccrc)
+
+
+def o_decompress_chunked_f64(ct, enc, n, chunk, eb, add_min=True, fixed_type=-1, fixed_mask20=0):
+    out = np.empty(n, dtype=np.float64)
+    s = np.ascontiguousarray(enc["stream"], dtype=np.uint8)
+    if s.size == 0:
+        s = np.zeros(1, np.uint8)
+    offs = np.ascontiguousarray(enc["offsets"], dtype=np.uint64)
+    cmin = _f64(enc["chunk_min"])
+    m20 = np.ascontiguousarray(enc["chunk_mask20"], dtype=np.uint32)
+    ctype = np.ascontiguousarray(enc["chunk_type"], dtype=np.int32)
+    rc = oracle().dco_decompress_chunked_f64(ct, _ptr(s), _ptr(offs), n, chunk, eb, int(add_min), _ptr(cmin), fixed_type,
+                                             fixed_mask20, _ptr(m20), _ptr(ctype), _ptr(out))
+    if rc:
+        raise ValueError("oracle: malformed stream (rc=%d)" % rc)
+    return out
+
+
+class RefLibF64:
+    """The reference's float64 entry points (impl/dataCompression.h), called as impl/k-means.c:520-590 calls them."""
+    _ENC = {CT_BITWISE: "myCompress_bitwise_double", CT_NP: "myCompress_bitwise_double_np",
+            CT_OP: "myCompress_bitwise_double_op", CT_MASK: "myCompress_bitwise_double_mask"}
+    _DEC = {CT_BITWISE: "myDecompress_bitwise_double", CT_NP: "myDecompress_bitwise_double_np",
+            CT_OP: "myDecompress_bitwise_double_op", CT_MASK: "myDecompress_bitwise_double_mask"}
+
+    def __init__(self, eb):
+        self.base = RefLib(eb)
+        lib = self.lib = self.base.lib
+        enc = [_f64p, C.c_int, C.POINTER(_u8p), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        dec = [_u8p, C.c_int, C.c_int]
+        for name in (self._ENC[CT_BITWISE], self._ENC[CT_NP], self._ENC[CT_OP]):
+            getattr(lib, name).argtypes = enc
+            getattr(lib, name).restype = None
+        lib.myCompress_bitwise_double_mask.argtypes = enc + [C.c_int, C.c_char_p]
+        lib.myCompress_bitwise_double_mask.restype = None
+        for name in (self._DEC[CT_BITWISE], self._DEC[CT_NP], self._DEC[CT_OP]):
+            getattr(lib, name).argtypes = dec
+            getattr(lib, name).restype = _f64p
+        lib.myDecompress_bitwise_double_mask.argtypes = dec + [C.c_int, C.c_char_p]
+        lib.myDecompress_bitwise_double_mask.restype = _f64p
+        lib.toSmallDataset_double.argtypes = [_f64p, C.POINTER(_f64p), C.c_int]
+        lib.toSmallDataset_double.restype = C.c_double
+        lib.med_dataset_double.argtypes = [_f64p, C.c_int, C.POINTER(C.c_int)]
+        lib.med_dataset_double.restype = C.c_double
+
+    @staticmethod
+    def mask_chars(mask20):
+        return ("{:020b}".format(mask20)).encode()
+
+    def min_subtract(self, x):
+        x = _f64(x)
+        p = _f64p()
+        mn = self.lib.toSmallDataset_double(x.ctypes.data_as(_f64p), C.byref(p), x.size)
+        y = np.ctypeslib.as_array(p, shape=(x.size,)).copy()
+        _libc.free(p)
+        return np.float64(mn), y
+
+    def med(self, x, type0=0):
+        x = _f64(x)
+        t = C.c_int(type0)
+        med = self.lib.med_dataset_double(x.ctypes.data_as(_f64p), x.size, C.byref(t))
+        return np.float64(med), t.value
+
+    def compress(self, ct, x, type_=0, mask20=0):
+        x = _f64(x)
+        bits, nbytes, pos = _u8p(), C.c_int(0), C.c_int(8)
+        args = [x.ctypes.data_as(_f64p), x.size, C.byref(bits), C.byref(nbytes), C.byref(pos)]
+        if ct == CT_MASK:
+            args += [type_, self.mask_chars(mask20)]
+        getattr(self.lib, self._ENC[ct])(*args)
+        out = np.ctypeslib.as_array(bits, shape=(nbytes.value,)).copy() if nbytes.value else np.zeros(0, np.uint8)
+        if nbytes.value:
+            _libc.free(bits)
+        return out, pos.value
+
+    def decompress(self, ct, stream, n, type_=0, mask20=0, pad=True):
+        """pad: one zero byte, for the same reason as RefLib.decompress (a 12-bit / zero-payload last code)."""
+        s = np.ascontiguousarray(stream, dtype=np.uint8)
+        if pad:
+            s = np.concatenate([s, np.zeros(1, np.uint8)])
+        args = [s.ctypes.data_as(_u8p), s.size, n]
+        if ct == CT_MASK:
+            args += [type_, self.mask_chars(mask20)]
+        p = getattr(self.lib, self._DEC[ct])(*args)
+        out = np.ctypeslib.as_array(p, shape=(n,)).copy()
+        _libc.free(p)
+        return out
+
+
+def ref_mask_decode_defined_f64(type_, mask20, eb):
+    """Where the reference's float64 CT=7 DECODER is well defined (dataCompression.c:1290-1296, :1355): the float32
+    rule with 9 -> 12: 2 <= type <= 9; escape payload m == 0 or m > 8; no escape of total length 12."""
+    n_eb = o_n_eb(eb)
+    m = min(max(n_eb + ((mask20 >> 8) & 0x7FF) - 1023, 0), 52)
+    if not (2 <= type_ <= 9):
+        return False
+    if 0 < m <= 8:
+        return False
+    k0 = max(m - 8, 0)
+    return (type_ + 2 + k0 != 12) and (type_ + 2 + m != 12)
