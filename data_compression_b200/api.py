@@ -29,7 +29,8 @@ EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb",
            "dcb_max_stream_bytes", "dcb_workspace_bytes", "dcb_compress", "dcb_decompress", "dcb_crc32_chunks",
            "dcb_chunk_stats", "dcb_chunk_medium", "dcb_flip_bits", "dcb_compress_host", "dcb_decompress_host",
            "dcb_last_stream_bits", "dcb_gather_face", "dcb_scatter_face", "dcb_himeno_jacobi",
-           "dcb_himeno_copy_interior"]
+           "dcb_himeno_copy_interior", "dcb_max_stream_bytes_f64", "dcb_workspace_bytes_f64", "dcb_compress_f64",
+           "dcb_decompress_f64"]
 
 _lib = None
 
@@ -73,6 +74,13 @@ def lib():
         L.dcb_himeno_copy_interior.argtypes = [vp, vp] + [i32] * 6 + [vp]
         L.dcb_scatter_face.restype = i32
         L.dcb_scatter_face.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, C.c_float, vp]
+        for f in ("dcb_max_stream_bytes_f64", "dcb_workspace_bytes_f64"):
+            getattr(L, f).restype = u64
+            getattr(L, f).argtypes = [u64, u64]
+        L.dcb_compress_f64.restype = i32
+        L.dcb_compress_f64.argtypes = [i32, vp, u64, u64, dbl, u32, i32, u32, vp, u64, vp, vp, vp, vp, vp, vp, vp, u64, vp]
+        L.dcb_decompress_f64.restype = i32
+        L.dcb_decompress_f64.argtypes = [i32, vp, vp, u64, u64, dbl, u32, i32, u32, vp, vp, vp, vp, vp, vp]
         L.dcb_compress_host.restype = i32
         L.dcb_compress_host.argtypes = [i32, vp, u64, u64, dbl, u32, i32, u32, vp, vp, vp, vp, vp, vp]
         L.dcb_decompress_host.restype = i32
@@ -201,6 +209,103 @@ def decompress(comp, out=None, status=None):
                                   _ptr(comp.chunk_min), _ptr(comp.chunk_medium), _ptr(comp.chunk_type), _ptr(out),
                                   _ptr(status), _cur_stream(dev))
     check(rc, "dcb_decompress")
+    return out
+
+
+# ---- float64 codecs (the reference's *_double entry points, impl/k-means.c / mm.c / lu.c) ----------
+def mask20_of(medium):
+    """First 1+11+8 bits of `medium`: the char mask[20] of impl/k-means.c:527-530."""
+    return int(np.array([medium], dtype=np.float64).view(np.uint64)[0] >> np.uint64(44))
+
+
+@dataclass
+class CompressedF64:
+    ct: int
+    n: int
+    chunk_elems: int
+    abs_error_bound: float
+    flags: int
+    fixed_type: int
+    fixed_mask20: int
+    stream: "object"                  # uint8 [capacity]
+    chunk_offsets: "object"           # int64 [K+1]
+    chunk_min: Optional["object"]     # float64 [K]
+    chunk_mask20: Optional["object"]  # int32 [K] (CT=7/9 per-chunk mask)
+    chunk_type: Optional["object"]    # int32 [K]
+    chunk_medium: Optional["object"]  # float64 [K] (only with exact_medium)
+    chunk_crc: Optional["object"]     # int32 [K]
+
+    @property
+    def num_chunks(self):
+        return self.chunk_offsets.numel() - 1
+
+    def total_bytes(self):
+        return int(self.chunk_offsets[-1].item())
+
+    def ratio(self):
+        return 8.0 * self.n / max(self.total_bytes(), 1)
+
+
+class WorkspaceF64:
+    def __init__(self, n, chunk_elems, device):
+        import torch
+        L = lib()
+        K = L.dcb_num_chunks(n, chunk_elems)
+        self.K = K
+        self.capacity = L.dcb_max_stream_bytes_f64(n, chunk_elems)
+        self.stream = torch.empty(self.capacity, dtype=torch.uint8, device=device)
+        self.offsets = torch.zeros(K + 1, dtype=torch.int64, device=device)
+        self.cmin = torch.zeros(max(K, 1), dtype=torch.float64, device=device)
+        self.cmed = torch.zeros(max(K, 1), dtype=torch.float64, device=device)
+        self.cmask = torch.zeros(max(K, 1), dtype=torch.int32, device=device)
+        self.ctype = torch.zeros(max(K, 1), dtype=torch.int32, device=device)
+        self.ccrc = torch.zeros(max(K, 1), dtype=torch.int32, device=device)
+        self.ws_bytes = L.dcb_workspace_bytes_f64(n, chunk_elems)
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=device)
+
+
+def compress_f64(x, ct=CT_BITWISE, abs_error_bound=1e-6, chunk_elems=DEFAULT_CHUNK, subtract_min=True,
+                 fixed_type=None, fixed_mask20=None, crc=False, workspace=None, exact_medium=False):
+    """x: contiguous float64 CUDA tensor.  One chunk == one reference call myCompress_bitwise_double*(..., (NULL,0,8))."""
+    import torch
+    if not (x.is_cuda and x.dtype == torch.float64 and x.is_contiguous()):
+        raise DcbError("compress_f64() needs a contiguous float64 CUDA tensor (there is no CPU path)")
+    n = x.numel()
+    ws = workspace or WorkspaceF64(n, chunk_elems, x.device)
+    flags = (F_SUBTRACT_MIN if subtract_min else 0) | (F_CRC if crc else 0) | (F_EXACT_MEDIUM if exact_medium else 0)
+    ft, fm = 0, 0
+    if fixed_type is not None:
+        flags |= F_FIXED_MASK
+        ft, fm = int(fixed_type), int(fixed_mask20)
+    with torch.cuda.device(x.device):
+        rc = lib().dcb_compress_f64(ct, _ptr(x), n, chunk_elems, abs_error_bound, flags, ft, fm, _ptr(ws.stream),
+                                    ws.capacity, _ptr(ws.offsets), _ptr(ws.cmin), _ptr(ws.cmask), _ptr(ws.ctype),
+                                    _ptr(ws.cmed), _ptr(ws.ccrc), _ptr(ws.ws), ws.ws_bytes, _cur_stream(x.device))
+    check(rc, "dcb_compress_f64")
+    has_crc = crc or ct in (CT_BITWISE_CRC, CT_MASK_CRC)
+    per_chunk_mask = ct in (CT_BITWISE_MASK, CT_MASK_CRC) and fixed_type is None
+    return CompressedF64(ct, n, chunk_elems, abs_error_bound, flags, ft, fm, ws.stream, ws.offsets,
+                         ws.cmin if subtract_min else None, ws.cmask if per_chunk_mask else None,
+                         ws.ctype if per_chunk_mask else None, ws.cmed if (per_chunk_mask and exact_medium) else None,
+                         ws.ccrc if has_crc else None)
+
+
+def decompress_f64(comp, out=None, status=None):
+    import torch
+    dev = comp.stream.device
+    if out is None:
+        out = torch.empty(comp.n, dtype=torch.float64, device=dev)
+    own_status = status is None
+    if own_status:
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib().dcb_decompress_f64(comp.ct, _ptr(comp.stream), _ptr(comp.chunk_offsets), comp.n, comp.chunk_elems,
+                                      comp.abs_error_bound, comp.flags & 3, comp.fixed_type, comp.fixed_mask20,
+                                      _ptr(comp.chunk_min), _ptr(comp.chunk_mask20), _ptr(comp.chunk_type), _ptr(out),
+                                      _ptr(status), _cur_stream(dev))
+    check(rc, "dcb_decompress_f64")
+    if own_status and int(status.item()) != 0:
+        raise DcbError("dcb_decompress_f64: malformed stream (status %d)" % int(status.item()))
     return out
 
 

@@ -15,6 +15,7 @@
 #include "dcb_stats.cuh"
 #include "dcb_crc.cuh"
 #include "dcb_face.cuh"
+#include "dcb_f64.cuh"
 static int ensure_crc_tables(cudaStream_t st);
 #include <math.h>
 #include <stdio.h>
@@ -315,6 +316,118 @@ extern "C" int dcb_scatter_face(float* d_p, int MI, int MJ, int MK, int ijk, int
   if (!d_p || !d_in || face_args(MI, MJ, MK, ijk, v, imax, jmax, kmax, &f)) return DCB_EINVAL;
   const size_t n = (size_t)f.A * f.B;
   dcb_scatter_face_kernel<<<(unsigned)((n + 255) / 256 < 4096 ? (n + 255) / 256 : 4096), 256, 0, (cudaStream_t)stream>>>(d_p, f, d_in, add);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+
+// ---- float64 codecs -----------------------------------------------------------------------------
+extern "C" uint64_t dcb_max_stream_bytes_f64(uint64_t n, uint64_t chunk) { (void)chunk; return 8 * n + 16; }
+extern "C" uint64_t dcb_workspace_bytes_f64(uint64_t n, uint64_t chunk) { (void)chunk; return 256 + 8 * num_tiles(n); }
+
+static int f64_setup(int ct, double eb, uint32_t* flags, int* bct, F64Const* k) {
+  *bct = base_ct(ct, flags);
+  k->eb = eb; k->n_eb = dcb_n_eb(eb);
+  if (*bct < 0 || !(eb > 0.0) || k->n_eb < 0) return DCB_EINVAL;
+  return DCB_OK;
+}
+
+extern "C" int dcb_compress_f64(int ct, const double* d_in, uint64_t n, uint64_t chunk, double eb, uint32_t flags,
+                                int fixed_type, uint32_t fixed_mask20, uint8_t* d_stream, uint64_t capacity,
+                                uint64_t* d_offsets, double* d_cmin, uint32_t* d_cmask, int32_t* d_ctype, double* d_cmedium,
+                                uint32_t* d_ccrc, void* d_ws, uint64_t ws_bytes, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  cudaStream_t st = (cudaStream_t)stream;
+  F64Args a;
+  memset(&a, 0, sizeof a);
+  int bct;
+  if (f64_setup(ct, eb, &flags, &bct, &a.k) != DCB_OK || !d_offsets) return DCB_EINVAL;
+  if (n == 0) { CK(cudaMemsetAsync(d_offsets, 0, sizeof(uint64_t), st)); return DCB_OK; }
+  const bool single = single_chunk(n, chunk);
+  if (!single && (chunk % DCB_TILE) != 0) return DCB_EINVAL;
+  if (!d_in || !d_stream || ((uintptr_t)d_stream & 15) || ((uintptr_t)d_in & 7)) return DCB_EINVAL;
+  if (n >= (1ull << 40) || (!single && chunk >= (1ull << 32))) return DCB_EINVAL;
+  const uint64_t K = dcb_num_chunks(n, chunk);
+  const bool per_chunk_mask = (bct == CT_MASK) && !(flags & DCB_F_FIXED_MASK);
+  if ((flags & DCB_F_SUBTRACT_MIN) && !d_cmin) return DCB_EINVAL;
+  if (per_chunk_mask && (!d_cmask || !d_ctype)) return DCB_EINVAL;
+  if ((flags & DCB_F_EXACT_MEDIUM) && per_chunk_mask && !d_cmedium) return DCB_EINVAL;
+  if ((flags & DCB_F_FIXED_MASK) && (fixed_type < 0 || fixed_type > 10 || fixed_mask20 >= (1u << 20))) return DCB_EINVAL;
+  if ((flags & DCB_F_CRC) && !d_ccrc) return DCB_EINVAL;
+  if (capacity < dcb_max_stream_bytes_f64(n, chunk)) return DCB_ECAPACITY;
+  if (!d_ws || ws_bytes < dcb_workspace_bytes_f64(n, chunk)) return DCB_ECAPACITY;
+
+  a.in = d_in; a.n = n; a.chunk = single ? n : chunk;
+  a.num_tiles = (uint32_t)(single ? num_tiles(n) : 0);
+  a.tiles_per_chunk = single ? (uint32_t)num_tiles(n) : (uint32_t)(chunk / DCB_TILE);
+  if (!single) a.num_tiles = (uint32_t)((K - 1) * a.tiles_per_chunk + num_tiles(n - (K - 1) * chunk));
+  a.num_chunks = K;
+  a.flags = flags & 15u; a.fixed_type = fixed_type; a.fixed_mask20 = fixed_mask20;
+  a.out = d_stream; a.offsets = d_offsets; a.cmin = d_cmin; a.cmask = per_chunk_mask ? d_cmask : nullptr; a.ctype = d_ctype;
+  a.tile_bits = (unsigned long long*)((char*)d_ws + 256);
+
+  if ((flags & DCB_F_SUBTRACT_MIN) || per_chunk_mask) {
+    F64StatsArgs s;
+    s.in = d_in; s.n = n; s.chunk = a.chunk; s.subtract_min = (flags & DCB_F_SUBTRACT_MIN) ? 1 : 0;
+    s.want_mask = per_chunk_mask ? 1 : 0;
+    s.cmin = d_cmin; s.cmask = d_cmask; s.ctype = d_ctype;
+    s.cmedium = (per_chunk_mask && (flags & DCB_F_EXACT_MEDIUM)) ? d_cmedium : nullptr;
+    dcb_f64_stats_kernel<<<(unsigned)K, F64_NT, 0, st>>>(s);
+    CK(cudaGetLastError());
+  }
+  switch (bct) {
+    case CT_BITWISE: dcb_f64_length_kernel<CT_BITWISE><<<a.num_tiles, F64_NT, 0, st>>>(a); break;
+    case CT_NP: dcb_f64_length_kernel<CT_NP><<<a.num_tiles, F64_NT, 0, st>>>(a); break;
+    case CT_MASK: dcb_f64_length_kernel<CT_MASK><<<a.num_tiles, F64_NT, 0, st>>>(a); break;
+    default: dcb_f64_length_kernel<CT_OP><<<a.num_tiles, F64_NT, 0, st>>>(a); break;
+  }
+  CK(cudaGetLastError());
+  dcb_f64_scan_kernel<<<1, 1024, 0, st>>>(a);
+  CK(cudaGetLastError());
+  dcb_f64_zero_kernel<<<(unsigned)num_sms() * 8, 256, 0, st>>>((uint32_t*)d_stream, d_offsets + K);
+  CK(cudaGetLastError());
+  switch (bct) {
+    case CT_BITWISE: dcb_f64_pack_kernel<CT_BITWISE><<<a.num_tiles, F64_NT, 0, st>>>(a); break;
+    case CT_NP: dcb_f64_pack_kernel<CT_NP><<<a.num_tiles, F64_NT, 0, st>>>(a); break;
+    case CT_MASK: dcb_f64_pack_kernel<CT_MASK><<<a.num_tiles, F64_NT, 0, st>>>(a); break;
+    default: dcb_f64_pack_kernel<CT_OP><<<a.num_tiles, F64_NT, 0, st>>>(a); break;
+  }
+  CK(cudaGetLastError());
+  if (flags & DCB_F_CRC) {
+    { int rc_ = ensure_crc_tables(st); if (rc_) return rc_; }
+    dcb_crc_kernel<<<(unsigned)((K + 3) / 4), 128, 0, st>>>(d_stream, d_offsets, K, d_ccrc);
+    CK(cudaGetLastError());
+  }
+  return DCB_OK;
+}
+
+extern "C" int dcb_decompress_f64(int ct, const uint8_t* d_stream, const uint64_t* d_offsets, uint64_t n, uint64_t chunk,
+                                  double eb, uint32_t flags, int fixed_type, uint32_t fixed_mask20, const double* d_cmin,
+                                  const uint32_t* d_cmask, const int32_t* d_ctype, double* d_out, int32_t* d_status,
+                                  void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  cudaStream_t st = (cudaStream_t)stream;
+  F64DecArgs a;
+  memset(&a, 0, sizeof a);
+  int bct;
+  if (f64_setup(ct, eb, &flags, &bct, &a.k) != DCB_OK) return DCB_EINVAL;
+  if (d_status) CK(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
+  if (n == 0) return DCB_OK;
+  const bool single = single_chunk(n, chunk);
+  if (!d_stream || !d_offsets || !d_out || ((uintptr_t)d_stream & 3)) return DCB_EINVAL;
+  const bool per_chunk_mask = (bct == CT_MASK) && !(flags & DCB_F_FIXED_MASK);
+  if ((flags & DCB_F_SUBTRACT_MIN) && !d_cmin) return DCB_EINVAL;
+  if (per_chunk_mask && (!d_cmask || !d_ctype)) return DCB_EINVAL;
+  if ((flags & DCB_F_FIXED_MASK) && (fixed_type < 0 || fixed_type > 10 || fixed_mask20 >= (1u << 20))) return DCB_EINVAL;
+  a.stream = d_stream; a.offsets = d_offsets; a.n = n; a.chunk = single ? n : chunk; a.num_chunks = dcb_num_chunks(n, chunk);
+  a.flags = flags & 15u; a.fixed_type = fixed_type; a.fixed_mask20 = fixed_mask20;
+  a.cmin = d_cmin; a.cmask = d_cmask; a.ctype = d_ctype; a.out = d_out; a.status = d_status;
+  const unsigned grid = (unsigned)((a.num_chunks + 127) / 128);
+  switch (bct) {
+    case CT_BITWISE: dcb_f64_decode_kernel<CT_BITWISE><<<grid, 128, 0, st>>>(a); break;
+    case CT_NP: dcb_f64_decode_kernel<CT_NP><<<grid, 128, 0, st>>>(a); break;
+    case CT_MASK: dcb_f64_decode_kernel<CT_MASK><<<grid, 128, 0, st>>>(a); break;
+    default: dcb_f64_decode_kernel<CT_OP><<<grid, 128, 0, st>>>(a); break;
+  }
   CK(cudaGetLastError());
   return DCB_OK;
 }

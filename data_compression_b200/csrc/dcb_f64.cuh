@@ -1,0 +1,413 @@
+// dcb_f64.cuh -- float64 variants of the bit-wise codecs: the reference's *_double functions
+// (impl/dataCompression.c: myCompress_bitwise_double :3189, _np :2633, _op :355, _mask :1590; myDecompress_bitwise_double
+// :2656, _np :2286, _op :476, _mask :1199; toSmallDataset_double :3522; med_dataset_double :3564) behind dcb_compress_f64 /
+// dcb_decompress_f64.  Same stream rules as float32 with the IEEE double layout: raw code = 12 + m bits,
+// m = clamp(n_eb + E - 1023, 0, 52); CT=7 mask = the first 1+11+8 = 20 bits of the chunk mean; predictors in double, every
+// operation rounded on its own.
+//
+// First version of this row: correct and parallel, not yet tuned like the float32 path.
+//   stats  : one block per chunk -- min (first occurrence wins, as the reference's '<' scan), then max / tree sum of
+//            x - min; the 20 mask bits come from the tree sum when its error bracket cannot change them, else from the exact
+//            sequential sum (one thread).
+//   length : one block per 4096-element tile -- classify every value, sum the code lengths.
+//   scan   : one block -- chunk byte offsets and every tile's bit offset.
+//   pack   : one block per tile -- classify again, bit offsets by a block scan, codes OR-ed into a shared-memory image of
+//            the tile's words, image copied out (the two boundary words with atomicOr into the zeroed stream).
+//   decode : one thread per chunk (a chunk is sequential by construction: predictors read the decoded history).
+#pragma once
+#include "dcb_common.cuh"
+
+#define F64_TILE 4096u
+#define F64_NT 256
+#define F64_PER 16
+#define F64_PITCH 17          // doubles per thread slot in the staged tile (16 + 1: conflict-free column reads)
+
+struct F64Const { double eb; int n_eb; };
+
+struct F64Args {
+  const double* in; uint64_t n; uint64_t chunk;        // chunk = elements per chunk (n for a single chunk)
+  uint32_t num_tiles; uint32_t tiles_per_chunk;        // every chunk has tiles_per_chunk tiles (the last one may have fewer)
+  uint64_t num_chunks;
+  uint32_t flags; int fixed_type; uint32_t fixed_mask20;
+  F64Const k;
+  uint8_t* out; uint64_t* offsets; double* cmin; uint32_t* cmask; int32_t* ctype;
+  unsigned long long* tile_bits;                       // [num_tiles]: code bits of the tile, then (after the scan) its bit offset
+};
+
+__device__ __forceinline__ int f64_mant_bits(uint64_t u, int n_eb) {
+  const int m = n_eb + (int)((u >> 52) & 0x7FFu) - 1023;
+  return min(max(m, 0), 52);
+}
+
+// compress_bitwise_double :3446-3477
+__device__ __forceinline__ void f64_raw(uint64_t u, int n_eb, uint64_t& code, int& len) {
+  len = 12 + f64_mant_bits(u, n_eb);
+  code = u >> (64 - len);
+}
+
+// compress_bitwise_double_mask :1493-1588
+__device__ __forceinline__ void f64_mask(uint64_t u, int n_eb, int type, uint32_t mask20, uint64_t& code, int& len) {
+  if ((uint32_t)(u >> 52) != (mask20 >> 8)) { f64_raw(u, n_eb, code, len); return; }
+  const int m = f64_mant_bits(u, n_eb);
+  const uint64_t prefix = (1ull << type) - 1ull;
+  const bool same8 = ((uint32_t)(u >> 44) & 0xFFu) == (mask20 & 0xFFu);
+  const int k = same8 ? max(m - 8, 0) : m;
+  const uint64_t payload = k ? ((u >> (52 - m)) & ((1ull << k) - 1ull)) : 0ull;
+  code = (((prefix << 1) | (same8 ? 0ull : 1ull)) << k) | payload;
+  len = type + 2 + k;
+}
+
+// one element of myCompress_bitwise_double{,_np,_op,_mask}: the exact -1 "empty slot" state machine (:3204-3222, :3260-3262)
+template <int CT>
+__device__ __forceinline__ void f64_classify(double v, double& b3, double& b2, double& b1, const F64Const& k, int type,
+                                             uint32_t mask20, uint64_t& code, int& len) {
+  const uint64_t u = (uint64_t)__double_as_longlong(v);
+  if (CT == CT_NP) { f64_raw(u, k.n_eb, code, len); return; }
+  int c3 = 0;
+  if (b3 == -1.0 || b2 == -1.0 || b1 == -1.0) {
+    if (fabs(v) < k.eb) c3 = 4;
+    if (b3 == -1.0) b3 = v; else if (b2 == -1.0) b2 = v; else if (b1 == -1.0) b1 = v;
+  } else {
+    const double p2 = __dsub_rn(__dmul_rn(2.0, b1), b2);
+    const double p3 = __dadd_rn(__dsub_rn(__dmul_rn(3.0, b1), __dmul_rn(3.0, b2)), b3);
+    const double d1 = fabs(__dsub_rn(b1, v)), d2 = fabs(__dsub_rn(p2, v)), d3 = fabs(__dsub_rn(p3, v));
+    double dmin = d1; int sel = 5;
+    if (d2 < dmin) { dmin = d2; sel = 6; }
+    if (d3 < dmin) { dmin = d3; sel = 7; }
+    b3 = b2; b2 = b1; b1 = v;
+    if (fabs(v) < k.eb) c3 = 4;
+    else if (dmin <= k.eb) c3 = sel;
+  }
+  if (c3) { code = (uint64_t)c3; len = 3; }
+  else if (CT == CT_BITWISE) f64_raw(u, k.n_eb, code, len);
+  else if (CT == CT_OP) { code = u; len = 64; }
+  else f64_mask(u, k.n_eb, type, mask20, code, len);
+}
+
+// tile geometry: tile t -> chunk, first element, count
+__device__ __forceinline__ void f64_tile_geom(const F64Args& a, uint32_t t, uint64_t& c, uint64_t& chunk_lo, uint64_t& e0,
+                                              uint32_t& cnt) {
+  c = t / a.tiles_per_chunk;
+  const uint32_t j = t - (uint32_t)c * a.tiles_per_chunk;
+  chunk_lo = c * a.chunk;
+  const uint64_t chunk_hi = min(a.n, chunk_lo + a.chunk);
+  e0 = chunk_lo + (uint64_t)j * F64_TILE;
+  cnt = (uint32_t)min((uint64_t)F64_TILE, chunk_hi - e0);
+}
+
+// the history a thread starts from at chunk-local position e0 - chunk_lo: the reference's state after the elements before
+// it = the last three values that are not the -1 marker, with b1 = -1 if the value just before was the marker
+__device__ __forceinline__ void f64_entry_state(const double* __restrict__ x, uint64_t chunk_lo, uint64_t g, double mn,
+                                                bool sub, double& b3, double& b2, double& b1) {
+  double r[3]; int cnt = 0; bool last_sent = false;
+  for (uint64_t i = g; i > chunk_lo && cnt < 3; ) {
+    --i;
+    const double v = sub ? __dsub_rn(x[i], mn) : x[i];
+    if (i + 1 == g) last_sent = (v == -1.0);
+    if (v != -1.0) r[cnt++] = v;
+  }
+  b3 = b2 = b1 = -1.0;
+  if (cnt == 3) { if (last_sent) { b3 = r[1]; b2 = r[0]; } else { b3 = r[2]; b2 = r[1]; b1 = r[0]; } }
+  else if (cnt == 2) { b3 = r[1]; b2 = r[0]; }
+  else if (cnt == 1) { b3 = r[0]; }
+}
+
+// ---- stats: toSmallDataset_double (:3522) + med_dataset_double (:3564) per chunk ------------------------------------
+struct F64StatsArgs {
+  const double* in; uint64_t n; uint64_t chunk; int subtract_min; int want_mask;
+  double* cmin; uint32_t* cmask; int32_t* ctype; double* cmedium;   // cmedium may be NULL
+};
+
+__device__ __forceinline__ bool f64_min_better(double av, uint64_t ai, double bv, uint64_t bi) {
+  // sequential scan with '<' from data[0]: a NaN never replaces, an equal value (also -0 == +0) never replaces
+  if (av != av) return false;
+  if (bv != bv) return true;
+  return (av < bv) || (av == bv && ai < bi);
+}
+
+__global__ void __launch_bounds__(F64_NT) dcb_f64_stats_kernel(F64StatsArgs s) {
+  __shared__ double sh_v[F64_NT / 32]; __shared__ unsigned long long sh_i[F64_NT / 32];
+  __shared__ double sh_a[F64_NT / 32], sh_b[F64_NT / 32]; __shared__ double sh_mn;
+  const uint64_t c = blockIdx.x, lo = c * s.chunk, hi = min(s.n, lo + s.chunk);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const double* x = s.in;
+  double mn = 0.0;
+  if (s.subtract_min) {
+    double bv = __longlong_as_double(0x7FF8000000000000ll); uint64_t bi = ~0ull;
+    for (uint64_t i = lo + 1 + tid; i < hi; i += F64_NT) { const double v = x[i]; if (f64_min_better(v, i, bv, bi)) { bv = v; bi = i; } }
+    for (int o = 16; o; o >>= 1) {
+      const double ov = __shfl_xor_sync(0xffffffffu, bv, o); const uint64_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (f64_min_better(ov, oi, bv, bi)) { bv = ov; bi = oi; }
+    }
+    if (lane == 0) { sh_v[warp] = bv; sh_i[warp] = bi; }
+    __syncthreads();
+    if (tid == 0) {
+      double m = x[lo];                                   // data[0]; a NaN here stays (every '<' is false)
+      if (m == m) {
+        uint64_t mi = lo;
+        for (int w = 0; w < F64_NT / 32; w++) if (f64_min_better(sh_v[w], sh_i[w], m, mi)) { m = sh_v[w]; mi = sh_i[w]; }
+      }
+      sh_mn = m; s.cmin[c] = m;
+    }
+    __syncthreads();
+    mn = sh_mn;
+  }
+  if (!s.want_mask) return;
+  const bool sub = s.subtract_min != 0;
+  // max with '>' from data[0] (NaN never replaces; a NaN data[0] stays), tree sum and sum of magnitudes
+  double mx = __longlong_as_double(0x7FF8000000000000ll), sum = 0.0, mag = 0.0;
+  for (uint64_t i = lo + tid; i < hi; i += F64_NT) {
+    const double y = sub ? __dsub_rn(x[i], mn) : x[i];
+    sum = __dadd_rn(sum, y); mag = __dadd_rn(mag, fabs(y));
+    if (y == y && (mx != mx || y > mx)) mx = y;
+  }
+  for (int o = 16; o; o >>= 1) {
+    sum = __dadd_rn(sum, __shfl_xor_sync(0xffffffffu, sum, o)); mag = __dadd_rn(mag, __shfl_xor_sync(0xffffffffu, mag, o));
+    const double om = __shfl_xor_sync(0xffffffffu, mx, o);
+    if (om == om && (mx != mx || om > mx)) mx = om;
+  }
+  if (lane == 0) { sh_v[warp] = mx; sh_a[warp] = sum; sh_b[warp] = mag; }
+  __syncthreads();
+  if (tid == 0) {
+    double M = sh_v[0], S = sh_a[0], G = sh_b[0];
+    for (int w = 1; w < F64_NT / 32; w++) {
+      S = __dadd_rn(S, sh_a[w]); G = __dadd_rn(G, sh_b[w]);
+      if (sh_v[w] == sh_v[w] && (M != M || sh_v[w] > M)) M = sh_v[w];
+    }
+    const double y0 = sub ? __dsub_rn(x[lo], mn) : x[lo];
+    if (y0 != y0) M = y0;                                 // max = data[0] = NaN: every later '>' is false
+    int type = 0, add = 0;                                // :3576-3585; 0 = "left at the caller's initial value"
+    for (int i = 10; i > 0; i--) {
+      add += 1 << i;
+      if (M < __longlong_as_double((long long)add << 52)) { type = 11 - i; break; }
+    }
+    s.ctype[c] = type;
+    const double cnt = (double)(int)(hi - lo);
+    const double E = __dmul_rn(__dmul_rn(cnt, 2.220446049250313e-16), G);      // n * 2^-52 * sum|y| >= |seq - tree|
+    const double mlo = __ddiv_rn(__dsub_rn(S, E), cnt), mhi = __ddiv_rn(__dadd_rn(S, E), cnt);
+    const uint32_t klo = (uint32_t)((uint64_t)__double_as_longlong(mlo) >> 44), khi = (uint32_t)((uint64_t)__double_as_longlong(mhi) >> 44);
+    const bool decided = (klo == khi) && (G == G) && (G < 1.0e300) && s.cmedium == nullptr;
+    if (decided) s.cmask[c] = klo;
+    if (!decided) {                                        // exact: total += data[i] in index order (:3568-3571)
+      double total = 0.0;
+      for (uint64_t i = lo; i < hi; i++) total = __dadd_rn(total, sub ? __dsub_rn(x[i], mn) : x[i]);
+      const double med = __ddiv_rn(total, cnt);
+      s.cmask[c] = (uint32_t)((uint64_t)__double_as_longlong(med) >> 44);
+      if (s.cmedium) s.cmedium[c] = med;
+    }
+  }
+}
+
+// ---- classification of one tile: thread t owns elements [16t, 16t+16) of the tile -------------------------------------
+// stage: the tile's values (min already subtracted) in shared memory, slot pitch 17 doubles
+template <int CT>
+__device__ __forceinline__ uint32_t f64_tile_codes(const F64Args& a, double* stage, uint64_t chunk_lo, uint64_t e0, uint32_t cnt,
+                                                   double mn, int type, uint32_t mask20, uint64_t (&code)[F64_PER],
+                                                   int (&len)[F64_PER]) {
+  const int tid = threadIdx.x;
+  const bool sub = (a.flags & DCB_F_SUBTRACT_MIN) != 0;
+  for (uint32_t e = tid; e < cnt; e += F64_NT) {                                 // coalesced
+    const double v = a.in[e0 + e];
+    stage[(e >> 4) * F64_PITCH + (e & 15)] = sub ? __dsub_rn(v, mn) : v;
+  }
+  __syncthreads();
+  const uint32_t my0 = (uint32_t)tid * F64_PER;
+  uint32_t bits = 0;
+  double b3 = -1.0, b2 = -1.0, b1 = -1.0;
+  if (CT != CT_NP && my0 < cnt) f64_entry_state(a.in, chunk_lo, e0 + my0, mn, sub, b3, b2, b1);
+  #pragma unroll
+  for (int j = 0; j < F64_PER; j++) {
+    code[j] = 0; len[j] = 0;
+    if (my0 + j < cnt) {
+      f64_classify<CT>(stage[tid * F64_PITCH + j], b3, b2, b1, a.k, type, mask20, code[j], len[j]);
+      bits += (uint32_t)len[j];
+    }
+  }
+  return bits;
+}
+
+__device__ __forceinline__ void f64_chunk_params(const F64Args& a, uint64_t c, double& mn, int& type, uint32_t& mask20) {
+  mn = (a.flags & DCB_F_SUBTRACT_MIN) ? a.cmin[c] : 0.0;
+  type = a.fixed_type; mask20 = a.fixed_mask20;
+  if (a.cmask && !(a.flags & DCB_F_FIXED_MASK)) { type = a.ctype[c]; mask20 = a.cmask[c]; }
+}
+
+template <int CT>
+__global__ void __launch_bounds__(F64_NT) dcb_f64_length_kernel(F64Args a) {
+  __shared__ double stage[F64_NT * F64_PITCH];
+  __shared__ uint32_t part[F64_NT / 32];
+  uint64_t c, chunk_lo, e0; uint32_t cnt;
+  f64_tile_geom(a, blockIdx.x, c, chunk_lo, e0, cnt);
+  double mn; int type; uint32_t mask20;
+  f64_chunk_params(a, c, mn, type, mask20);
+  uint64_t code[F64_PER]; int len[F64_PER];
+  uint32_t bits = f64_tile_codes<CT>(a, stage, chunk_lo, e0, cnt, mn, type, mask20, code, len);
+  bits = __reduce_add_sync(0xffffffffu, bits);
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = bits;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int w = 0; w < F64_NT / 32; w++) t += part[w];
+    a.tile_bits[blockIdx.x] = t;
+  }
+}
+
+// ---- scan: chunk byte offsets and tile bit offsets; one block, thread i owns a contiguous run of chunks ----------------
+__global__ void __launch_bounds__(1024) dcb_f64_scan_kernel(F64Args a) {
+  __shared__ unsigned long long base[1024];
+  const uint64_t K = a.num_chunks, per = (K + 1023) / 1024;
+  const uint64_t c0 = min(K, (uint64_t)threadIdx.x * per), c1 = min(K, c0 + per);
+  unsigned long long mine = 0;
+  for (uint64_t c = c0; c < c1; c++) {
+    unsigned long long b = 0;
+    const uint64_t t0 = c * a.tiles_per_chunk, t1 = min((uint64_t)a.num_tiles, t0 + a.tiles_per_chunk);
+    for (uint64_t t = t0; t < t1; t++) b += a.tile_bits[t];
+    mine += (b + 7) >> 3;
+  }
+  base[threadIdx.x] = mine;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long run = 0;
+    for (int i = 0; i < 1024; i++) { const unsigned long long v = base[i]; base[i] = run; run += v; }
+    a.offsets[K] = run;
+  }
+  __syncthreads();
+  unsigned long long off = base[threadIdx.x];
+  for (uint64_t c = c0; c < c1; c++) {
+    a.offsets[c] = off;
+    unsigned long long bit = off * 8ull;
+    const uint64_t t0 = c * a.tiles_per_chunk, t1 = min((uint64_t)a.num_tiles, t0 + a.tiles_per_chunk);
+    for (uint64_t t = t0; t < t1; t++) { const unsigned long long b = a.tile_bits[t]; a.tile_bits[t] = bit; bit += b; }
+    off += (bit - off * 8ull + 7) >> 3;
+  }
+}
+
+// zero the words the pack kernel ORs into: [0, total + 8) rounded to words
+__global__ void dcb_f64_zero_kernel(uint32_t* __restrict__ out, const uint64_t* __restrict__ total_bytes) {
+  const uint64_t words = (*total_bytes + 11) >> 2;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (uint64_t)gridDim.x * blockDim.x) out[i] = 0u;
+}
+
+// ---- pack --------------------------------------------------------------------------------------------------------------
+#define F64_IMG_WORDS (F64_TILE * 2 + 8)
+template <int CT>
+__global__ void __launch_bounds__(F64_NT) dcb_f64_pack_kernel(F64Args a) {
+  __shared__ __align__(16) unsigned char smem_raw[F64_NT * F64_PITCH * 8];          // staged tile, then the word image
+  __shared__ uint32_t part[F64_NT / 32];
+  static_assert(F64_IMG_WORDS * 4 <= F64_NT * F64_PITCH * 8, "image must fit the staging buffer");
+  double* stage = reinterpret_cast<double*>(smem_raw);
+  uint32_t* img = reinterpret_cast<uint32_t*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  uint64_t c, chunk_lo, e0; uint32_t cnt;
+  f64_tile_geom(a, blockIdx.x, c, chunk_lo, e0, cnt);
+  double mn; int type; uint32_t mask20;
+  f64_chunk_params(a, c, mn, type, mask20);
+  uint64_t code[F64_PER]; int len[F64_PER];
+  const uint32_t bits = f64_tile_codes<CT>(a, stage, chunk_lo, e0, cnt, mn, type, mask20, code, len);
+  uint32_t incl = bits;
+  #pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+  if (lane == 31) part[warp] = incl;
+  __syncthreads();                                                                 // also: every thread has read its stage slot
+  uint32_t wbase = 0, tile_bits = 0;
+  #pragma unroll
+  for (int w = 0; w < F64_NT / 32; w++) { const uint32_t v = part[w]; if (w < warp) wbase += v; tile_bits += v; }
+  const unsigned long long bit0 = a.tile_bits[blockIdx.x];                         // global bit offset of the tile
+  const uint32_t phase = (uint32_t)(bit0 & 31ull);
+  const uint32_t nwords = (phase + tile_bits + 31u) >> 5;
+  for (uint32_t w = tid; w < nwords; w += F64_NT) img[w] = 0u;
+  __syncthreads();
+  uint32_t pos = phase + wbase + incl - bits;
+  #pragma unroll
+  for (int j = 0; j < F64_PER; j++) {
+    if (len[j]) {
+      const uint64_t left = code[j] << (64 - len[j]);                              // left aligned
+      const uint32_t o = pos & 31u, wi = pos >> 5;
+      const uint64_t hi = left >> o;
+      const uint32_t lo = o ? (uint32_t)((left << (64 - o)) >> 32) : 0u;
+      const uint32_t w0 = (uint32_t)(hi >> 32), w1 = (uint32_t)hi;
+      if (w0) atomicOr(&img[wi], w0);
+      if (w1) atomicOr(&img[wi + 1], w1);
+      if (lo) atomicOr(&img[wi + 2], lo);
+      pos += (uint32_t)len[j];
+    }
+  }
+  __syncthreads();
+  uint32_t* gw = reinterpret_cast<uint32_t*>(a.out) + (bit0 >> 5);
+  for (uint32_t w = tid; w < nwords; w += F64_NT) {
+    const uint32_t v = __byte_perm(img[w], 0u, 0x0123);                            // stream bytes are MSB first
+    if (w == 0 || w + 1 == nwords) { if (v) atomicOr(gw + w, v); }
+    else gw[w] = v;
+  }
+}
+
+// ---- decode: one thread per chunk ---------------------------------------------------------------------------------------
+struct F64DecArgs {
+  const uint8_t* stream; const uint64_t* offsets; uint64_t n; uint64_t chunk; uint64_t num_chunks;
+  uint32_t flags; int fixed_type; uint32_t fixed_mask20; F64Const k;
+  const double* cmin; const uint32_t* cmask; const int32_t* ctype;
+  double* out; int32_t* status;
+};
+
+template <int CT>
+__global__ void __launch_bounds__(128) dcb_f64_decode_kernel(F64DecArgs a) {
+  const uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= a.num_chunks) return;
+  const uint64_t lo = c * a.chunk, cn = min(a.chunk, a.n - lo);
+  const uint32_t* __restrict__ s32 = reinterpret_cast<const uint32_t*>(a.stream);
+  const uint64_t end_word = (a.offsets[a.num_chunks] + 3) >> 2;                    // words past the stream read as 0
+  uint64_t pos = a.offsets[c] * 8ull;
+  const bool addmin = (a.flags & DCB_F_SUBTRACT_MIN) != 0;
+  const double mn = addmin ? a.cmin[c] : 0.0;
+  int type = a.fixed_type; uint32_t mask20 = a.fixed_mask20;
+  if (CT == CT_MASK && !(a.flags & DCB_F_FIXED_MASK)) { type = a.ctype[c]; mask20 = a.cmask[c]; }
+  const int m_mask = f64_mant_bits((uint64_t)mask20 << 44, a.k.n_eb);
+  double b3 = -1.0, b2 = -1.0, b1 = -1.0;
+  uint64_t cached = ~0ull; uint32_t w0 = 0, w1 = 0, w2 = 0;
+  for (uint64_t i = 0; i < cn; i++) {
+    const uint64_t wi = pos >> 5; const uint32_t o = (uint32_t)(pos & 31ull);
+    if (wi != cached) {
+      w0 = wi < end_word ? __byte_perm(s32[wi], 0u, 0x0123) : 0u;
+      w1 = wi + 1 < end_word ? __byte_perm(s32[wi + 1], 0u, 0x0123) : 0u;
+      w2 = wi + 2 < end_word ? __byte_perm(s32[wi + 2], 0u, 0x0123) : 0u;
+      cached = wi;
+    }
+    const uint64_t w = ((uint64_t)__funnelshift_l(w1, w0, o) << 32) | (uint64_t)__funnelshift_l(w2, w1, o);
+    double v; int len;
+    if (w >> 63) {
+      if (CT == CT_NP) { if (a.status) atomicExch(a.status, DCB_EFORMAT); return; }
+      len = 3;
+      const uint32_t sel = (uint32_t)(w >> 61) & 3u;
+      if (sel == 0) v = 0.0;
+      else if (sel == 1) v = b1;
+      else if (sel == 2) v = __dsub_rn(__dmul_rn(2.0, b1), b2);
+      else v = __dadd_rn(__dsub_rn(__dmul_rn(3.0, b1), __dmul_rn(3.0, b2)), b3);
+    } else if (CT == CT_OP) {
+      len = 64; v = __longlong_as_double((long long)w);
+    } else {
+      bool escape = false;
+      if (CT == CT_MASK) { const uint64_t ones = (1ull << type) - 1ull; escape = ((w >> (63 - type)) & ones) == ones; }
+      uint64_t top; int have;
+      if (!escape) {
+        have = 12 + f64_mant_bits(w, a.k.n_eb);
+        top = have == 64 ? w : (w & ~(~0ull >> have));
+        len = have;
+      } else {
+        const int flag = (int)((w >> (62 - type)) & 1ull);
+        const int k = flag ? m_mask : max(m_mask - 8, 0);
+        const int hdr = type + 2;
+        const uint64_t payload = k ? ((w << hdr) >> (64 - k)) : 0ull;
+        len = hdr + k;
+        if (flag) { top = ((uint64_t)(mask20 >> 8) << 52) | (k ? payload << (52 - k) : 0ull); have = 12 + k; }
+        else { top = ((uint64_t)mask20 << 44) | (k ? payload << (44 - k) : 0ull); have = 20 + k; }
+      }
+      v = __longlong_as_double((long long)(have >= 64 ? top : (top | (0x8000000000000000ull >> have))));
+    }
+    pos += (uint64_t)len;
+    a.out[lo + i] = addmin ? __dadd_rn(v, mn) : v;
+    if (CT != CT_NP) {
+      if (b3 == -1.0) b3 = v; else if (b2 == -1.0) b2 = v; else if (b1 == -1.0) b1 = v;
+      else { b3 = b2; b2 = b1; b1 = v; }
+    }
+  }
+}

@@ -94,6 +94,26 @@ int dcb_chunk_medium(const float* d_in, uint64_t n, float* d_medium, int32_t* d_
 /* bit_flip (dataCompression.c:5858) test hook: flips bit (7 - bit_index%8) of byte bit_index/8 for each index */
 int dcb_flip_bits(uint8_t* d_stream, const uint64_t* d_bit_indices, uint64_t count, void* cuda_stream);
 
+/* ---- float64 codecs: the reference's *_double entry points ------------------------------------
+ * dcb_compress_f64 replaces, per chunk, toSmallDataset_double (dataCompression.c:3522) -> [med_dataset_double (:3564) +
+ * the mask chars, impl/k-means.c:525-530] -> myCompress_bitwise_double (:3189) / _np (:2633) / _mask (:1590) / _op (:355)
+ * from (NULL,0,8) [-> do_crc32]; dcb_decompress_f64 replaces myDecompress_bitwise_double (:2656) / _np (:2286) / _mask
+ * (:1199) / _op (:476) and the "+ min" loop (impl/k-means.c:597-598).  Same arguments as the float32 calls except:
+ *   d_chunk_mask20[K] : the first 1+11+8 bits of the chunk mean (what the reference cuts out of doubletostr(medium));
+ *   d_chunk_medium[K] : the exact mean, written only with DCB_F_EXACT_MEDIUM (may be NULL otherwise);
+ *   fixed_type 0..10, fixed_mask20 < 2^20; worst case stream 8*n + 16 bytes. */
+uint64_t dcb_max_stream_bytes_f64(uint64_t n, uint64_t chunk_elems);
+uint64_t dcb_workspace_bytes_f64(uint64_t n, uint64_t chunk_elems);
+int dcb_compress_f64(int ct, const double* d_in, uint64_t n, uint64_t chunk_elems, double abs_error_bound,
+                     uint32_t flags, int fixed_type, uint32_t fixed_mask20,
+                     uint8_t* d_stream, uint64_t stream_capacity, uint64_t* d_chunk_offsets,
+                     double* d_chunk_min, uint32_t* d_chunk_mask20, int32_t* d_chunk_type, double* d_chunk_medium,
+                     uint32_t* d_chunk_crc, void* d_workspace, uint64_t workspace_bytes, void* cuda_stream);
+int dcb_decompress_f64(int ct, const uint8_t* d_stream, const uint64_t* d_chunk_offsets, uint64_t n,
+                       uint64_t chunk_elems, double abs_error_bound, uint32_t flags, int fixed_type,
+                       uint32_t fixed_mask20, const double* d_chunk_min, const uint32_t* d_chunk_mask20,
+                       const int32_t* d_chunk_type, double* d_out, int32_t* d_status, void* cuda_stream);
+
 /* Himeno halo faces, device resident.  dcb_gather_face replaces transform_3d_array_to_1d_array
  * (impl/dataCompression.c:3741-3775; p is float[MI][MJ][MK], ijk = 1/2/3 fixes i/j/k = v, the face has jmax*kmax /
  * imax*kmax / imax*jmax elements in the reference's loop order); dcb_scatter_face replaces the loops that write a
