@@ -30,7 +30,7 @@ EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb",
            "dcb_chunk_stats", "dcb_chunk_medium", "dcb_flip_bits", "dcb_compress_host", "dcb_decompress_host",
            "dcb_last_stream_bits", "dcb_gather_face", "dcb_scatter_face", "dcb_himeno_jacobi",
            "dcb_himeno_copy_interior", "dcb_max_stream_bytes_f64", "dcb_workspace_bytes_f64", "dcb_compress_f64",
-           "dcb_decompress_f64"]
+           "dcb_decompress_f64", "dcb_chunk_stats_f64"]
 
 _lib = None
 
@@ -79,6 +79,8 @@ def lib():
             getattr(L, f).argtypes = [u64, u64]
         L.dcb_compress_f64.restype = i32
         L.dcb_compress_f64.argtypes = [i32, vp, u64, u64, dbl, u32, i32, u32, vp, u64, vp, vp, vp, vp, vp, vp, vp, u64, vp]
+        L.dcb_chunk_stats_f64.restype = i32
+        L.dcb_chunk_stats_f64.argtypes = [vp, u64, u64, i32, i32, vp, vp, vp, vp, vp]
         L.dcb_decompress_f64.restype = i32
         L.dcb_decompress_f64.argtypes = [i32, vp, vp, u64, u64, dbl, u32, i32, u32, vp, vp, vp, vp, vp, vp]
         L.dcb_compress_host.restype = i32

@@ -364,6 +364,7 @@ extern "C" int dcb_compress_f64(int ct, const double* d_in, uint64_t n, uint64_t
   a.flags = flags & 15u; a.fixed_type = fixed_type; a.fixed_mask20 = fixed_mask20;
   a.out = d_stream; a.offsets = d_offsets; a.cmin = d_cmin; a.cmask = per_chunk_mask ? d_cmask : nullptr; a.ctype = d_ctype;
   a.tile_bits = (unsigned long long*)((char*)d_ws + 256);
+  a.last_bits = (unsigned long long*)d_ws;
 
   if ((flags & DCB_F_SUBTRACT_MIN) || per_chunk_mask) {
     F64StatsArgs s;
@@ -397,6 +398,21 @@ extern "C" int dcb_compress_f64(int ct, const double* d_in, uint64_t n, uint64_t
     dcb_crc_kernel<<<(unsigned)((K + 3) / 4), 128, 0, st>>>(d_stream, d_offsets, K, d_ccrc);
     CK(cudaGetLastError());
   }
+  return DCB_OK;
+}
+
+// toSmallDataset_double (:3522) / med_dataset_double (:3564) per chunk as a stand-alone pass.  want_medium: also mask20, type
+// and (d_chunk_medium != NULL) the exact sequential mean; subtract_min = 0 takes the values as they are.
+extern "C" int dcb_chunk_stats_f64(const double* d_in, uint64_t n, uint64_t chunk, int subtract_min, int want_medium,
+                                   double* d_cmin, uint32_t* d_cmask, int32_t* d_ctype, double* d_cmedium, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (!d_in || n == 0 || (subtract_min && !d_cmin) || (want_medium && (!d_cmask || !d_ctype))) return DCB_EINVAL;
+  const bool single = single_chunk(n, chunk);
+  F64StatsArgs s;
+  s.in = d_in; s.n = n; s.chunk = single ? n : chunk; s.subtract_min = subtract_min ? 1 : 0; s.want_mask = want_medium ? 1 : 0;
+  s.cmin = d_cmin; s.cmask = d_cmask; s.ctype = d_ctype; s.cmedium = d_cmedium;
+  dcb_f64_stats_kernel<<<(unsigned)dcb_num_chunks(n, chunk), F64_NT, 0, (cudaStream_t)stream>>>(s);
+  CK(cudaGetLastError());
   return DCB_OK;
 }
 

@@ -32,6 +32,7 @@ struct F64Args {
   F64Const k;
   uint8_t* out; uint64_t* offsets; double* cmin; uint32_t* cmask; int32_t* ctype;
   unsigned long long* tile_bits;                       // [num_tiles]: code bits of the tile, then (after the scan) its bit offset
+  unsigned long long* last_bits;                       // code bits of the LAST chunk (the legacy callers' `pos`)
 };
 
 __device__ __forceinline__ int f64_mant_bits(uint64_t u, int n_eb) {
@@ -278,6 +279,7 @@ __global__ void __launch_bounds__(1024) dcb_f64_scan_kernel(F64Args a) {
     unsigned long long bit = off * 8ull;
     const uint64_t t0 = c * a.tiles_per_chunk, t1 = min((uint64_t)a.num_tiles, t0 + a.tiles_per_chunk);
     for (uint64_t t = t0; t < t1; t++) { const unsigned long long b = a.tile_bits[t]; a.tile_bits[t] = bit; bit += b; }
+    if (c + 1 == K) *a.last_bits = bit - off * 8ull;
     off += (bit - off * 8ull + 7) >> 3;
   }
 }

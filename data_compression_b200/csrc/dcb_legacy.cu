@@ -200,3 +200,146 @@ extern "C" float strtofloat(char* str) {
   return f;
 }
 extern "C" int to_absErrorBound_binary(double absErrBound) { return dcb_n_eb(absErrBound); }
+
+// ================================ float64 symbols (k-means / MM / LU callers) ====================================
+// mask[1+11+8] of '0'/'1' chars (impl/k-means.c:527-530) -> the 20-bit integer the kernels take
+static uint32_t mask20_from_chars(const char* mask) {
+  uint32_t m = 0;
+  for (int i = 0; i < 20; i++) m = (m << 1) | (uint32_t)(mask[i] == '1');
+  return m;
+}
+
+static void legacy_compress_f64(int ct, double* data, int num, unsigned char** data_bits, int* bytes, int* pos, int type,
+                                const char* mask) {
+  if (num <= 0) return;
+  if (dcb_device_count() == 0) die("myCompress_bitwise_double* (no CUDA device)", DCB_ENODEVICE);
+  const uint64_t n = (uint64_t)num;
+  const uint64_t cap = dcb_max_stream_bytes_f64(n, 0), wsb = dcb_workspace_bytes_f64(n, 0);
+  DevBuf dx(n * 8), ds(cap), doff(16), dws(wsb);
+  if (!dx.p || !ds.p || !doff.p || !dws.p) die("cudaMalloc", DCB_ECUDA);
+  uint32_t flags = 0, m20 = 0;
+  if (ct == DCB_CT_BITWISE_MASK) { flags |= DCB_F_FIXED_MASK; m20 = mask20_from_chars(mask); }
+  cudaMemcpy(dx.p, data, n * 8, cudaMemcpyHostToDevice);
+  const int rc = dcb_compress_f64(ct, (const double*)dx.p, n, 0, dc_get_abs_error_bound(), flags, type, m20, (uint8_t*)ds.p, cap,
+                                  (uint64_t*)doff.p, NULL, NULL, NULL, NULL, NULL, dws.p, wsb, NULL);
+  if (rc != DCB_OK) die("dcb_compress_f64", rc);
+  uint64_t offs[2] = {0, 0};
+  unsigned long long nbits = 0;
+  cudaMemcpy(offs, doff.p, 16, cudaMemcpyDeviceToHost);
+  if (cudaMemcpy(&nbits, dws.p, 8, cudaMemcpyDeviceToHost) != cudaSuccess) die("myCompress_bitwise_double*", DCB_ECUDA);
+  unsigned char* tmp = (unsigned char*)malloc((size_t)(offs[1] ? offs[1] : 1));
+  if (!tmp) { printf("ERROR: Out of memory\n"); exit(1); }
+  if (cudaMemcpy(tmp, ds.p, (size_t)offs[1], cudaMemcpyDeviceToHost) != cudaSuccess) die("myCompress_bitwise_double*", DCB_ECUDA);
+  append_stream(data_bits, bytes, pos, tmp, nbits);
+  free(tmp);
+}
+
+static double* legacy_decompress_f64(int ct, unsigned char* data_bits, int bytes, int num, int type, const char* mask) {
+  double* out = (double*)malloc(sizeof(double) * (size_t)(num > 0 ? num : 1));
+  if (!out) { printf("ERROR: Out of memory\n"); exit(1); }
+  if (num <= 0) return out;
+  if (dcb_device_count() == 0) die("myDecompress_bitwise_double* (no CUDA device)", DCB_ENODEVICE);
+  const uint64_t n = (uint64_t)num, nb = (uint64_t)(bytes > 0 ? bytes : 0);
+  DevBuf ds(nb + 16), doff(16), dout(n * 8), dst(16);
+  if (!ds.p || !doff.p || !dout.p || !dst.p) die("cudaMalloc", DCB_ECUDA);
+  const uint64_t offs[2] = {0, nb};
+  uint32_t flags = 0, m20 = 0;
+  if (ct == DCB_CT_BITWISE_MASK) { flags |= DCB_F_FIXED_MASK; m20 = mask20_from_chars(mask); }
+  cudaMemset(ds.p, 0, (size_t)nb + 16);
+  cudaMemcpy(ds.p, data_bits, (size_t)nb, cudaMemcpyHostToDevice);
+  cudaMemcpy(doff.p, offs, 16, cudaMemcpyHostToDevice);
+  const int rc = dcb_decompress_f64(ct, (const uint8_t*)ds.p, (const uint64_t*)doff.p, n, 0, dc_get_abs_error_bound(), flags, type,
+                                    m20, NULL, NULL, NULL, (double*)dout.p, (int32_t*)dst.p, NULL);
+  if (rc != DCB_OK) die("dcb_decompress_f64", rc);
+  int32_t status = 0;
+  cudaMemcpy(&status, dst.p, 4, cudaMemcpyDeviceToHost);
+  if (cudaMemcpy(out, dout.p, n * 8, cudaMemcpyDeviceToHost) != cudaSuccess) die("myDecompress_bitwise_double*", DCB_ECUDA);
+  if (status == DCB_EFORMAT) { printf("Error leading bit 1\n"); exit(1); }
+  return out;
+}
+
+static int clamp_type_f64(int type) { return type < 0 ? 0 : (type > 10 ? 10 : type); }
+
+extern "C" void myCompress_bitwise_double(double data[], int num, unsigned char** data_bits, int* bytes, int* pos) {
+  legacy_compress_f64(DCB_CT_BITWISE, data, num, data_bits, bytes, pos, 0, NULL);
+}
+extern "C" double* myDecompress_bitwise_double(unsigned char* data_bits, int bytes, int num) {
+  return legacy_decompress_f64(DCB_CT_BITWISE, data_bits, bytes, num, 0, NULL);
+}
+extern "C" void myCompress_bitwise_double_np(double data[], int num, unsigned char** data_bits, int* bytes, int* pos) {
+  legacy_compress_f64(DCB_CT_BITWISE_NP, data, num, data_bits, bytes, pos, 0, NULL);
+}
+extern "C" double* myDecompress_bitwise_double_np(unsigned char* data_bits, int bytes, int num) {
+  return legacy_decompress_f64(DCB_CT_BITWISE_NP, data_bits, bytes, num, 0, NULL);
+}
+extern "C" void myCompress_bitwise_double_op(double data[], int num, unsigned char** data_bits, int* bytes, int* pos) {
+  legacy_compress_f64(DCB_CT_BITWISE_OP, data, num, data_bits, bytes, pos, 0, NULL);
+}
+extern "C" double* myDecompress_bitwise_double_op(unsigned char* data_bits, int bytes, int num) {
+  return legacy_decompress_f64(DCB_CT_BITWISE_OP, data_bits, bytes, num, 0, NULL);
+}
+extern "C" void myCompress_bitwise_double_mask(double data[], int num, unsigned char** data_bits, int* bytes, int* pos, int type,
+                                               char mask[1 + 11 + 8]) {
+  legacy_compress_f64(DCB_CT_BITWISE_MASK, data, num, data_bits, bytes, pos, clamp_type_f64(type), mask);
+}
+extern "C" double* myDecompress_bitwise_double_mask(unsigned char* data_bits, int bytes, int num, int type, char mask[1 + 11 + 8]) {
+  return legacy_decompress_f64(DCB_CT_BITWISE_MASK, data_bits, bytes, num, clamp_type_f64(type), mask);
+}
+
+__global__ void dcb_subtract_f64_kernel(const double* __restrict__ x, const double* __restrict__ mn, double* __restrict__ y, uint64_t n) {
+  const double m = *mn;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    y[i] = __dsub_rn(x[i], m);
+}
+
+// toSmallDataset_double, dataCompression.c:3522-3541
+extern "C" double toSmallDataset_double(double data[], double** data_small, int num) {
+  *data_small = (double*)malloc(sizeof(double) * (size_t)(num > 0 ? num : 1));
+  if (!*data_small) { printf("ERROR: Out of memory\n"); exit(1); }
+  if (num <= 0) return 0.0;
+  if (dcb_device_count() == 0) die("toSmallDataset_double (no CUDA device)", DCB_ENODEVICE);
+  const uint64_t n = (uint64_t)num;
+  DevBuf dx(n * 8), dy(n * 8), dm(16);
+  if (!dx.p || !dy.p || !dm.p) die("cudaMalloc", DCB_ECUDA);
+  double mn = 0.0;
+  cudaMemcpy(dx.p, data, n * 8, cudaMemcpyHostToDevice);
+  int rc = dcb_chunk_stats_f64((const double*)dx.p, n, 0, 1, 0, (double*)dm.p, NULL, NULL, NULL, NULL);
+  if (rc != DCB_OK) die("dcb_chunk_stats_f64", rc);
+  dcb_subtract_f64_kernel<<<1184, 256>>>((const double*)dx.p, (const double*)dm.p, (double*)dy.p, n);
+  cudaMemcpy(*data_small, dy.p, n * 8, cudaMemcpyDeviceToHost);
+  if (cudaMemcpy(&mn, dm.p, 8, cudaMemcpyDeviceToHost) != cudaSuccess) die("toSmallDataset_double", DCB_ECUDA);
+  return mn;
+}
+
+// med_dataset_double, dataCompression.c:3564-3591: exact sequential mean, max -> type (untouched when max >= 2^1023)
+extern "C" double med_dataset_double(double* data, int num, int* type) {
+  if (num <= 0) return 0.0;
+  if (dcb_device_count() == 0) die("med_dataset_double (no CUDA device)", DCB_ENODEVICE);
+  const uint64_t n = (uint64_t)num;
+  DevBuf dx(n * 8), dm(64);
+  if (!dx.p || !dm.p) die("cudaMalloc", DCB_ECUDA);
+  cudaMemcpy(dx.p, data, n * 8, cudaMemcpyHostToDevice);
+  double* d_med = (double*)dm.p; uint32_t* d_mask = (uint32_t*)((char*)dm.p + 16); int32_t* d_ty = (int32_t*)((char*)dm.p + 32);
+  int rc = dcb_chunk_stats_f64((const double*)dx.p, n, 0, 0, 1, NULL, d_mask, d_ty, d_med, NULL);
+  if (rc != DCB_OK) die("dcb_chunk_stats_f64", rc);
+  double med = 0.0; int32_t ty = 0;
+  cudaMemcpy(&med, d_med, 8, cudaMemcpyDeviceToHost);
+  if (cudaMemcpy(&ty, d_ty, 4, cudaMemcpyDeviceToHost) != cudaSuccess) die("med_dataset_double", DCB_ECUDA);
+  if (ty != 0) *type = ty;
+  return med;
+}
+
+// doubletostr / strtodbl, dataCompression.c (bit-string helpers the drivers use to build the mask, impl/k-means.c:526-530)
+extern "C" void doubletostr(double* a, char* str) {
+  uint64_t c;
+  memcpy(&c, a, 8);
+  for (int i = 0; i < 64; i++) str[i] = (char)('0' + ((c >> (63 - i)) & 1ull));
+  str[64] = '\0';
+}
+extern "C" double strtodbl(char* str) {
+  uint64_t c = 0;
+  for (int i = 0; i < 64; i++) c = (c << 1) + (uint64_t)(str[i] - '0');
+  double d;
+  memcpy(&d, &c, 8);
+  return d;
+}

@@ -1,4 +1,4 @@
-/* dataCompression_b200.h -- the reference's own float32 hot-path symbols, served by libdcb200.so.
+/* dataCompression_b200.h -- the reference's own float32 (and float64) hot-path symbols, served by libdcb200.so.
  *
  * Same names, same signatures, same ownership rules as impl/dataCompression.h of
  * smallcat9603/data-compression (the line each prototype replaces is cited), so that the MPI drivers
@@ -54,6 +54,23 @@ uint32_t do_crc32(unsigned char* data_bits, int bytes);                         
 void   floattostr(float* a, char* str);                                                                       /* dataCompression.h:125 */
 float  strtofloat(char* str);                                                                                 /* dataCompression.h:127 */
 int    to_absErrorBound_binary(double absErrBound);                                                           /* dataCompression.h:141 */
+
+
+/* ---- float64 variants (the k-means / MM / LU callers, impl/k-means.c:510-780, impl/mm.c:404-690, impl/lu.c:199-345) ---- */
+void    myCompress_bitwise_double(double data[], int num, unsigned char** data_bits, int* bytes, int* pos);   /* dataCompression.h:89 */
+double* myDecompress_bitwise_double(unsigned char* data_bits, int bytes, int num);                            /* dataCompression.h:84 */
+void    myCompress_bitwise_double_np(double data[], int num, unsigned char** data_bits, int* bytes, int* pos);/* dataCompression.h:76 */
+double* myDecompress_bitwise_double_np(unsigned char* data_bits, int bytes, int num);                         /* dataCompression.h:72 */
+void    myCompress_bitwise_double_op(double data[], int num, unsigned char** data_bits, int* bytes, int* pos);/* dataCompression.h:79 */
+double* myDecompress_bitwise_double_op(unsigned char* data_bits, int bytes, int num);                         /* dataCompression.h:80 */
+void    myCompress_bitwise_double_mask(double data[], int num, unsigned char** data_bits, int* bytes, int* pos,
+                                       int type, char mask[1 + 11 + 8]);                                      /* dataCompression.h:66 */
+double* myDecompress_bitwise_double_mask(unsigned char* data_bits, int bytes, int num, int type,
+                                         char mask[1 + 11 + 8]);                                              /* dataCompression.h:63 */
+double  toSmallDataset_double(double data[], double** data_small, int num);                                   /* dataCompression.h:95 */
+double  med_dataset_double(double* data, int num, int* type);                                                 /* dataCompression.h:98 */
+void    doubletostr(double* a, char* str);                                                                    /* dataCompression.h:126 */
+double  strtodbl(char* str);                                                                                  /* dataCompression.h:128 */
 
 #ifdef __cplusplus
 }

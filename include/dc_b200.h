@@ -109,6 +109,11 @@ int dcb_compress_f64(int ct, const double* d_in, uint64_t n, uint64_t chunk_elem
                      uint8_t* d_stream, uint64_t stream_capacity, uint64_t* d_chunk_offsets,
                      double* d_chunk_min, uint32_t* d_chunk_mask20, int32_t* d_chunk_type, double* d_chunk_medium,
                      uint32_t* d_chunk_crc, void* d_workspace, uint64_t workspace_bytes, void* cuda_stream);
+/* toSmallDataset_double (:3522) / med_dataset_double (:3564) per chunk as a stand-alone pass; after dcb_compress_f64 the first
+ * 8 bytes of d_workspace hold the code bits of the last chunk (the legacy `pos`). */
+int dcb_chunk_stats_f64(const double* d_in, uint64_t n, uint64_t chunk_elems, int subtract_min, int want_medium,
+                        double* d_chunk_min, uint32_t* d_chunk_mask20, int32_t* d_chunk_type, double* d_chunk_medium,
+                        void* cuda_stream);
 int dcb_decompress_f64(int ct, const uint8_t* d_stream, const uint64_t* d_chunk_offsets, uint64_t n,
                        uint64_t chunk_elems, double abs_error_bound, uint32_t flags, int fixed_type,
                        uint32_t fixed_mask20, const double* d_chunk_min, const uint32_t* d_chunk_mask20,

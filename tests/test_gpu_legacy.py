@@ -120,3 +120,70 @@ def test_append_to_existing_stream(L):
         tot = bits_a.size + bits_b.size
         assert st[2].value == (8 if tot % 8 == 0 else 8 - tot % 8)
     L.dc_set_abs_error_bound(1e-6)
+
+
+# ---- float64 symbols: the call sequence of impl/k-means.c:520-590 -------------------------------------------------
+_f64p = C.POINTER(C.c_double)
+ENC64 = {5: "myCompress_bitwise_double", 6: "myCompress_bitwise_double_np", 11: "myCompress_bitwise_double_op",
+         7: "myCompress_bitwise_double_mask"}
+DEC64 = {5: "myDecompress_bitwise_double", 6: "myDecompress_bitwise_double_np", 11: "myDecompress_bitwise_double_op",
+         7: "myDecompress_bitwise_double_mask"}
+
+
+@pytest.fixture(scope="module")
+def L64(L):
+    enc = [_f64p, C.c_int, C.POINTER(_u8p), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    dec = [_u8p, C.c_int, C.c_int]
+    for ct in (5, 6, 11):
+        getattr(L, ENC64[ct]).argtypes, getattr(L, ENC64[ct]).restype = enc, None
+        getattr(L, DEC64[ct]).argtypes, getattr(L, DEC64[ct]).restype = dec, _f64p
+    L.myCompress_bitwise_double_mask.argtypes, L.myCompress_bitwise_double_mask.restype = enc + [C.c_int, C.c_char_p], None
+    L.myDecompress_bitwise_double_mask.argtypes, L.myDecompress_bitwise_double_mask.restype = dec + [C.c_int, C.c_char_p], _f64p
+    L.toSmallDataset_double.argtypes, L.toSmallDataset_double.restype = [_f64p, C.POINTER(_f64p), C.c_int], C.c_double
+    L.med_dataset_double.argtypes, L.med_dataset_double.restype = [_f64p, C.c_int, C.POINTER(C.c_int)], C.c_double
+    L.doubletostr.argtypes = [_f64p, C.c_char_p]
+    L.strtodbl.argtypes, L.strtodbl.restype = [C.c_char_p], C.c_double
+    return L
+
+
+def test_kmeans_call_sequence_f64(L64):
+    L = L64
+    rng = np.random.default_rng(64)
+    datasets = [np.sort(rng.random(100) * 1000.0), rng.random(8192) * 10, np.full(5000, 2.5),
+                np.cumsum(rng.standard_normal(20001)) * 0.01 + 7.0, np.array([3.25])]
+    for eb in (0.01, 1e-6):
+        L.dc_set_abs_error_bound(eb)
+        for x in datasets:
+            p = _f64p()
+            mn = L.toSmallDataset_double(x.ctypes.data_as(_f64p), C.byref(p), x.size)
+            y = np.ctypeslib.as_array(p, shape=(x.size,)).copy()
+            _libc.free(p)
+            omn, oy = ol.o_min_subtract_f64(x)
+            assert np.float64(mn) == omn and np.array_equal(y.view(np.uint64), oy.view(np.uint64))
+            t = C.c_int(0)
+            med = np.float64(L.med_dataset_double(y.ctypes.data_as(_f64p), y.size, C.byref(t)))
+            omed, ot = ol.o_med_f64(y, 0)
+            assert med.view(np.uint64) == omed.view(np.uint64) and t.value == ot       # exact sequential mean
+            s = C.create_string_buffer(65)
+            L.doubletostr(C.byref(C.c_double(float(med))), s)
+            mask = s.value[:20]                                                         # impl/k-means.c:527-530
+            assert int(mask, 2) == ol.mask20_of(med)
+            assert np.float64(L.strtodbl(s.value)).view(np.uint64) == med.view(np.uint64)
+            for ct in (5, 6, 11, 7):
+                bits, nbytes, pos = _u8p(), C.c_int(0), C.c_int(8)
+                args = [y.ctypes.data_as(_f64p), y.size, C.byref(bits), C.byref(nbytes), C.byref(pos)]
+                if ct == 7:
+                    args += [t.value, mask]
+                getattr(L, ENC64[ct])(*args)
+                got = np.ctypeslib.as_array(bits, shape=(nbytes.value,)).copy()
+                want, wpos = ol.o_compress_f64(ct, y, eb, t.value, ol.mask20_of(med))
+                assert nbytes.value == want.size and pos.value == wpos, (ct, eb, x.size)
+                assert np.array_equal(got, want), (ct, eb, x.size)
+                dargs = [bits, nbytes.value, y.size] + ([t.value, mask] if ct == 7 else [])
+                dp = getattr(L, DEC64[ct])(*dargs)
+                dec = np.ctypeslib.as_array(dp, shape=(y.size,)).copy()
+                _libc.free(dp)
+                _libc.free(bits)
+                odec = ol.o_decompress_f64(ct, want, y.size, eb, t.value, ol.mask20_of(med))
+                assert np.array_equal(dec.view(np.uint64), odec.view(np.uint64)), (ct, eb, x.size)
+    L.dc_set_abs_error_bound(1e-6)
