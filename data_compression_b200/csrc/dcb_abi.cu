@@ -11,6 +11,7 @@
 #include "../../include/dc_b200.h"
 #include "dcb_common.cuh"
 #include "dcb_encode.cuh"
+#include "dcb_encode_slots.cuh"
 #include "dcb_decode.cuh"
 #include "dcb_stats.cuh"
 #include "dcb_crc.cuh"
@@ -79,9 +80,22 @@ extern "C" uint64_t dcb_num_chunks(uint64_t n, uint64_t chunk) {
 }
 extern "C" uint64_t dcb_max_stream_bytes(uint64_t n, uint64_t chunk) { (void)chunk; return 4 * n + 16; }
 static uint64_t num_tiles(uint64_t n) { return (n + DCB_TILE - 1) / DCB_TILE; }
+// "one chunk == one tile": min / medium are fused in the encoder and blocks are independent (slot path)
+static bool chunk_is_tile(uint64_t n, uint64_t chunk) {
+  return num_tiles(n) == 1 || (!single_chunk(n, chunk) && chunk == DCB_TILE);
+}
+// workspace layout: [0,256) header (ticket, scanner claim, last_bits @8, last_tile_bits @16) | status[tiles] u64
+//   slot path only:  | gsum[G] u32 | sizes[K] u32 | pad to 256 | K slots of DCB_SLOT_PITCH bytes
+static uint64_t ws_head_bytes(uint64_t n) { return 256 + 8 * num_tiles(n); }
+static uint64_t ws_groups(uint64_t K) { return (K + DCB_GROUP - 1) / DCB_GROUP; }
+static uint64_t ws_slots_at(uint64_t n) {
+  const uint64_t K = num_tiles(n);
+  return (ws_head_bytes(n) + 4 * ws_groups(K) + 4 * K + 255) & ~(uint64_t)255;
+}
+static bool g_force_single_pass = getenv("DCB_SINGLE_PASS") != nullptr;    // A/B switch: the coupled single-pass encoder
 extern "C" uint64_t dcb_workspace_bytes(uint64_t n, uint64_t chunk) {
-  (void)chunk;
-  return 256 + 8 * num_tiles(n);
+  if (n && chunk_is_tile(n, chunk)) return ws_slots_at(n) + num_tiles(n) * (uint64_t)DCB_SLOT_PITCH;
+  return ws_head_bytes(n);
 }
 
 static int g_num_sms = 0;
@@ -108,6 +122,22 @@ static cudaError_t launch_encode(const EncArgs& a, cudaStream_t st) {
   // one block becomes the prefix scanner, the others are workers
   const unsigned grid = 1u + (unsigned)min((uint64_t)a.num_tiles, (uint64_t)num_sms() * DCB_ENC_BLOCKS_PER_SM - 1u);
   dcb_encode_kernel<CT><<<grid, DCB_NT, sizeof(EncSmem), st>>>(a);
+  return cudaGetLastError();
+}
+
+template <int CT>
+static cudaError_t launch_encode_slots(const EncArgs& a, const CompactArgs& ca, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(dcb_encode_slots_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SlotSmem));
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const unsigned grid = (unsigned)min((uint64_t)a.num_tiles, (uint64_t)num_sms() * DCB_SLOT_BLOCKS_PER_SM);
+  dcb_encode_slots_kernel<CT><<<grid, DCB_NT, sizeof(SlotSmem), st>>>(a);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  dcb_compact_kernel<<<(unsigned)ws_groups(ca.K), DCB_COMPACT_NT, 0, st>>>(ca);
   return cudaGetLastError();
 }
 
@@ -176,8 +206,34 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
   if (((uintptr_t)d_in & 15) == 0) a.flags |= DCB_ENC_IN_ALIGNED;
 
   // a chunk is "one tile" when every chunk fits a single thread block: min / medium are fused in the encoder
-  const bool chunk_is_tile = (a.tiles_per_chunk == 1) || (a.num_tiles == 1);
-  if (!chunk_is_tile) {
+  const bool is_tile = chunk_is_tile(n, chunk);
+  if (is_tile && !g_force_single_pass) {
+    // slot path: independent blocks write fixed-pitch slots, a second kernel builds the chunk table and compacts
+    char* ws = (char*)d_ws;
+    a.last_tile_bits = (uint32_t*)(ws + 16);
+    a.gsum = (uint32_t*)(ws + ws_head_bytes(n));
+    a.sizes = a.gsum + ws_groups(K);
+    a.slots = (uint8_t*)(ws + ws_slots_at(n));
+    CK(cudaMemsetAsync(d_ws, 0, (size_t)(ws_head_bytes(n) + 4 * ws_groups(K)), st));
+    CompactArgs ca;
+    ca.slots = a.slots; ca.sizes = a.sizes; ca.gsum = a.gsum; ca.last_tile_bits = a.last_tile_bits; ca.K = K;
+    ca.out = d_stream; ca.offsets = d_offsets; ca.last_bits = a.last_bits;
+    cudaError_t es;
+    switch (bct) {
+      case CT_BITWISE: es = launch_encode_slots<CT_BITWISE>(a, ca, st); break;
+      case CT_NP: es = launch_encode_slots<CT_NP>(a, ca, st); break;
+      case CT_MASK: es = launch_encode_slots<CT_MASK>(a, ca, st); break;
+      default: es = launch_encode_slots<CT_OP>(a, ca, st); break;
+    }
+    CK(es);
+    if (flags & DCB_F_CRC) {
+      { int rc_ = ensure_crc_tables(st); if (rc_) return rc_; }
+      dcb_crc_kernel<<<(unsigned)((K + 3) / 4), 128, 0, st>>>(d_stream, d_offsets, K, d_ccrc);
+      CK(cudaGetLastError());
+    }
+    return DCB_OK;
+  }
+  if (!is_tile) {
     // tile boundaries inside a chunk fall on arbitrary BITS: boundary words are OR-ed into a zeroed stream
     a.flags |= DCB_ENC_ATOMIC_OUT;
     CK(cudaMemsetAsync(d_stream, 0, (size_t)(4 * n + 16), st));
@@ -191,7 +247,7 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
       a.flags |= DCB_ENC_STATS_READY;
     }
   }
-  CK(cudaMemsetAsync(d_ws, 0, (size_t)dcb_workspace_bytes(n, chunk), st));
+  CK(cudaMemsetAsync(d_ws, 0, (size_t)ws_head_bytes(n), st));
   cudaError_t e;
   switch (bct) {
     case CT_BITWISE: e = launch_encode<CT_BITWISE>(a, st); break;

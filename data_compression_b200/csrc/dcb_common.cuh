@@ -48,6 +48,11 @@ struct EncArgs {
   unsigned int* ticket;
   unsigned int* scanner_claim;    // 0 -> 1 by the first block that runs: it becomes the prefix scanner
   unsigned long long* last_bits;  // bit length of the whole stream before the final byte round-up (legacy `pos`)
+  // slot path (dcb_encode_slots.cuh): one chunk == one tile, blocks are independent
+  uint8_t* slots;                 // [K] scratch slots of DCB_SLOT_PITCH bytes
+  uint32_t* sizes;                // [K] bytes of every chunk
+  uint32_t* gsum;                 // [ceil(K / DCB_GROUP)] bytes of every group of chunks (zeroed before the launch)
+  uint32_t* last_tile_bits;       // code bits of the last chunk
 };
 
 struct DecArgs {
