@@ -12,6 +12,7 @@
 #include "dcb_common.cuh"
 #include "dcb_encode.cuh"
 #include "dcb_encode_slots.cuh"
+#include "dcb_encode_warp.cuh"
 #include "dcb_decode.cuh"
 #include "dcb_stats.cuh"
 #include "dcb_crc.cuh"
@@ -92,7 +93,19 @@ static uint64_t ws_slots_at(uint64_t n) {
   const uint64_t K = num_tiles(n);
   return (ws_head_bytes(n) + 4 * ws_groups(K) + 4 * K + 255) & ~(uint64_t)255;
 }
-static bool g_force_single_pass = getenv("DCB_SINGLE_PASS") != nullptr;    // A/B switch: the coupled single-pass encoder
+// Encoder for one-tile chunks.  Default (3): the warp-autonomous kernel for CT=5/6/11, the block-per-chunk slot kernel for
+// CT=7 (its medium needs block-wide exact sums; measured faster there).  DCB_ENCODER = warp | slots | single forces one
+// kernel for every CT (A/B runs, and the parity tests cover all three).
+static int encoder_choice() {
+  static const int v = [] {
+    const char* e = getenv("DCB_ENCODER");
+    if (getenv("DCB_SINGLE_PASS") || (e && !strcmp(e, "single"))) return 0;
+    if (e && !strcmp(e, "slots")) return 1;
+    if (e && !strcmp(e, "warp")) return 2;
+    return 3;
+  }();
+  return v;
+}
 extern "C" uint64_t dcb_workspace_bytes(uint64_t n, uint64_t chunk) {
   if (n && chunk_is_tile(n, chunk)) return ws_slots_at(n) + num_tiles(n) * (uint64_t)DCB_SLOT_PITCH;
   return ws_head_bytes(n);
@@ -122,6 +135,24 @@ static cudaError_t launch_encode(const EncArgs& a, cudaStream_t st) {
   // one block becomes the prefix scanner, the others are workers
   const unsigned grid = 1u + (unsigned)min((uint64_t)a.num_tiles, (uint64_t)num_sms() * DCB_ENC_BLOCKS_PER_SM - 1u);
   dcb_encode_kernel<CT><<<grid, DCB_NT, sizeof(EncSmem), st>>>(a);
+  return cudaGetLastError();
+}
+
+template <int CT>
+static cudaError_t launch_encode_warp(const EncArgs& a, const CompactArgs& ca, cudaStream_t st) {
+  static bool attr_set = false;
+  const int smem = (int)(sizeof(WarpBuf) * (DCB_NT / 32));
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(dcb_encode_warp_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const uint64_t blocks = ((uint64_t)a.num_tiles + DCB_NT / 32 - 1) / (DCB_NT / 32);
+  const unsigned grid = (unsigned)min(blocks, (uint64_t)num_sms() * DCB_SLOT_BLOCKS_PER_SM);
+  dcb_encode_warp_kernel<CT><<<grid, DCB_NT, smem, st>>>(a);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  dcb_compact_kernel<<<(unsigned)ws_groups(ca.K), DCB_COMPACT_NT, 0, st>>>(ca);
   return cudaGetLastError();
 }
 
@@ -207,7 +238,7 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
 
   // a chunk is "one tile" when every chunk fits a single thread block: min / medium are fused in the encoder
   const bool is_tile = chunk_is_tile(n, chunk);
-  if (is_tile && !g_force_single_pass) {
+  if (is_tile && encoder_choice() != 0) {
     // slot path: independent blocks write fixed-pitch slots, a second kernel builds the chunk table and compacts
     char* ws = (char*)d_ws;
     a.last_tile_bits = (uint32_t*)(ws + 16);
@@ -219,11 +250,20 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
     ca.slots = a.slots; ca.sizes = a.sizes; ca.gsum = a.gsum; ca.last_tile_bits = a.last_tile_bits; ca.K = K;
     ca.out = d_stream; ca.offsets = d_offsets; ca.last_bits = a.last_bits;
     cudaError_t es;
-    switch (bct) {
-      case CT_BITWISE: es = launch_encode_slots<CT_BITWISE>(a, ca, st); break;
-      case CT_NP: es = launch_encode_slots<CT_NP>(a, ca, st); break;
-      case CT_MASK: es = launch_encode_slots<CT_MASK>(a, ca, st); break;
-      default: es = launch_encode_slots<CT_OP>(a, ca, st); break;
+    if (encoder_choice() == 2 || (encoder_choice() == 3 && bct != CT_MASK)) {
+      switch (bct) {
+        case CT_BITWISE: es = launch_encode_warp<CT_BITWISE>(a, ca, st); break;
+        case CT_NP: es = launch_encode_warp<CT_NP>(a, ca, st); break;
+        case CT_MASK: es = launch_encode_warp<CT_MASK>(a, ca, st); break;
+        default: es = launch_encode_warp<CT_OP>(a, ca, st); break;
+      }
+    } else {
+      switch (bct) {
+        case CT_BITWISE: es = launch_encode_slots<CT_BITWISE>(a, ca, st); break;
+        case CT_NP: es = launch_encode_slots<CT_NP>(a, ca, st); break;
+        case CT_MASK: es = launch_encode_slots<CT_MASK>(a, ca, st); break;
+        default: es = launch_encode_slots<CT_OP>(a, ca, st); break;
+      }
     }
     CK(es);
     if (flags & DCB_F_CRC) {

@@ -1,0 +1,562 @@
+// dcb_encode_warp.cuh -- WARP-AUTONOMOUS encoder for "one chunk == one 4096-element tile" (CT=5/6/7/11), pass 1 of the slot
+// path (dcb_encode_slots.cuh; pass 2 = dcb_compact_kernel).  Replaces, per chunk, toSmallDataset_float (dataCompression.c:3543)
+// -> [med_dataset_float (:3593)] -> myCompress_bitwise{,_np,_mask,_op} (:3310, :2645, :2030, :577).
+//
+// One warp owns one chunk from the first load to the last store; nothing is shared between warps, so there is no
+// __syncthreads, no shared-memory reduction and no cross-warp fix-up at all (the block-per-chunk kernel spent 18-27 % of its
+// warp time at its two barriers and a third of its instructions on per-tile bookkeeping, profiles/r1_summary.md).
+//   * the chunk is consumed in 8 ROUNDS of 512 elements, 16 consecutive elements per lane (a lane concatenates its own codes
+//     in registers; the 3-element look-back comes from the neighbour lane by shuffle, from the previous round by three
+//     carried registers);
+//   * statistics (min, [max, raw sum], NaN/Inf/huge test) of the NEXT chunk are folded in one round at a time from a 2 KB
+//     cp.async staging buffer -- that is also what pulls the next chunk from HBM into L2, so the transposing cp.async of
+//     the classification pass hits L2; every load has a whole round (~2 us) to land;
+//   * a round's codes are packed into a 2 KB warp buffer at the bit position where the previous round stopped, whole words
+//     leave for the chunk's scratch slot at once (MSB-first bytes, coalesced), the open word is carried in a register.
+#pragma once
+#include "dcb_encode_slots.cuh"
+
+#define DCB_WR 512                  // elements per round (32 lanes x 16)
+#define DCB_WWORDS 520              // words of the round buffer: 512 codes of <= 32 bits + carry word + slack
+
+struct WarpBuf {
+  float X[2][32 * DCB_XPITCH];      // classification pass: double-buffered rounds, one 80-byte slot per lane
+  float4 P[128];                    // statistics pass of the next chunk: one round, linear
+  uint32_t W[DCB_WWORDS];           // packed round
+};
+
+struct Pass1 {                      // per-lane partial statistics of a chunk
+  float mn, mx, s0, s1, ws, n0, n1;
+  uint32_t sg;
+};
+template <int CT>
+__device__ __forceinline__ void p1_reset(Pass1& p) {
+  p.mn = __uint_as_float(0x7f800000u); p.mx = __uint_as_float(0xff800000u);
+  p.s0 = 0.0f; p.s1 = 0.0f; p.ws = 0.0f; p.n0 = 0.0f; p.n1 = 0.0f; p.sg = 0u;
+}
+// four consecutive raw values; w = (elements of the chunk from the first of them on), the weight of the CT=7 bound.
+// nacc turns Inf/NaN iff one of them is NaN, Inf or >= 2^127 in magnitude (or, harmlessly, when the running sum of huge
+// values overflows: such chunks take the exact SLOW path).
+template <int CT, bool SG>
+__device__ __forceinline__ void p1_add4(Pass1& p, const float4 v, int which, float w) {
+  p.mn = fminf(fminf(p.mn, v.x), v.y); p.mn = fminf(fminf(p.mn, v.z), v.w);
+  if (CT == CT_MASK) {
+    p.mx = fmaxf(fmaxf(p.mx, v.x), v.y); p.mx = fmaxf(fmaxf(p.mx, v.z), v.w);
+    const float t = __fadd_rn(__fadd_rn(v.x, v.y), __fadd_rn(v.z, v.w));
+    if (which & 1) p.s1 = __fadd_rn(p.s1, t); else p.s0 = __fadd_rn(p.s0, t);
+    p.ws = __fmaf_rn(t, w, p.ws);
+  }
+  p.n0 = __fmaf_rn(fabsf(v.x), 2.0f, p.n0); p.n1 = __fmaf_rn(fabsf(v.y), 2.0f, p.n1);
+  p.n0 = __fmaf_rn(fabsf(v.z), 2.0f, p.n0); p.n1 = __fmaf_rn(fabsf(v.w), 2.0f, p.n1);
+  if (SG) p.sg |= f2u(v.x) | f2u(v.y) | f2u(v.z) | f2u(v.w);
+}
+template <int CT>
+__device__ __forceinline__ void p1_add1(Pass1& p, float v, bool submin) {      // ragged rounds, unaligned input
+  p.mn = fminf(p.mn, v);
+  if (CT == CT_MASK) { p.mx = fmaxf(p.mx, v); p.s0 = __fadd_rn(p.s0, v); }
+  p.n0 = __fmaf_rn(fabsf(v), 2.0f, p.n0);
+  if (!submin) p.sg |= f2u(v);
+}
+
+__device__ __forceinline__ bool round_is_bulk(const EncArgs& a, uint64_t e0, uint64_t cend) {
+  return e0 + DCB_WR <= cend && (a.flags & DCB_ENC_IN_ALIGNED);
+}
+// classification pass: round starting at element e0 -> one 80-byte slot per lane (16 consecutive elements each)
+__device__ __forceinline__ void warp_issue_x(const EncArgs& a, uint64_t e0, uint64_t cend, float* Xb, int lane, bool bulk) {
+  if (bulk) {
+    const float* g = a.in + e0;
+    #pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const int u = q * 32 + lane;
+      cp_async16(Xb + (u >> 2) * DCB_XPITCH + (u & 3) * 4, g + u * 4);
+    }
+  } else {
+    const uint64_t my0 = e0 + (uint64_t)lane * DCB_E;
+    float* slot = Xb + lane * DCB_XPITCH;
+    #pragma unroll
+    for (int e = 0; e < DCB_E; e++) slot[e] = (my0 + e < cend) ? __ldg(a.in + my0 + e) : 0.0f;
+  }
+}
+// statistics pass: the same round of the NEXT chunk, linear
+__device__ __forceinline__ void warp_issue_p(const EncArgs& a, uint64_t e0, float4* P, int lane, bool bulk) {
+  if (bulk) {
+    const float* g = a.in + e0;
+    #pragma unroll
+    for (int q = 0; q < 4; q++) cp_async16(&P[q * 32 + lane], g + (q * 32 + lane) * 4);
+  }
+}
+// j = round inside its chunk (weights: 4096 - index of the float4's first element; only used for whole bulk chunks)
+template <int CT>
+__device__ __forceinline__ void warp_consume_p(const EncArgs& a, uint64_t e0, uint64_t cend, const float4* P, int lane,
+                                               Pass1& p, bool submin, bool bulk, int j) {
+  if (bulk) {
+    const float w0 = (float)(DCB_TILE - j * DCB_WR - lane * 4);
+    if (submin) {
+      #pragma unroll
+      for (int q = 0; q < 4; q++) p1_add4<CT, false>(p, P[q * 32 + lane], q, w0 - (float)(q * 128));
+    } else {
+      #pragma unroll
+      for (int q = 0; q < 4; q++) p1_add4<CT, true>(p, P[q * 32 + lane], q, w0 - (float)(q * 128));
+    }
+  } else {
+    for (int k = 0; k < DCB_E; k++) {
+      const uint64_t idx = e0 + (uint64_t)k * 32 + lane;
+      if (idx < cend) p1_add1<CT>(p, __ldg(a.in + idx), submin);
+    }
+  }
+}
+// whole chunk at once (a warp's first chunk): direct loads
+template <int CT>
+__device__ __forceinline__ void pass1_direct(const EncArgs& a, uint64_t cbase, uint64_t cend, int lane, Pass1& p, bool submin) {
+  int j = 0;
+  for (uint64_t e0 = cbase; e0 < cend; e0 += 2 * DCB_WR, j += 2) {
+    if (round_is_bulk(a, e0 + DCB_WR, cend)) {           // two rounds: eight 128-bit loads in flight
+      const float4* g = reinterpret_cast<const float4*>(a.in + e0);
+      float4 v[8];
+      #pragma unroll
+      for (int q = 0; q < 8; q++) v[q] = __ldg(g + q * 32 + lane);
+      const float w0 = (float)(DCB_TILE - j * DCB_WR - lane * 4);
+      #pragma unroll
+      for (int q = 0; q < 8; q++) p1_add4<CT, true>(p, v[q], q, w0 - (float)(q * 128));
+    } else {
+      for (uint64_t idx = e0 + lane; idx < min(e0 + 2 * DCB_WR, cend); idx += 32) p1_add1<CT>(p, __ldg(a.in + idx), submin);
+    }
+  }
+}
+
+// med_dataset_float (:3593-3620), exactly, for the chunks whose mask bits the bound cannot pin (and SLOW chunks): one more
+// pass over the chunk in the classification layout.  While the running sum S stays inside one binade [2^e, 2^(e+1)) it
+// lives on the grid q = 2^(e-23), and S -> fl(S + y) commutes with shifts of S by 2q, so a lane whose 16 values provably
+// keep S inside one binade is a 2-state transducer S_out = S_in + d[parity(S_in / q)], d[0], d[1] from two 16-step chains
+// started at 2^e and 2^e + q -- all lanes in parallel, every d exact.  The binade is pinned by S at the start of the round
+// (exact, carried) plus a warp scan of the lanes' plain sums: the reference's running sum before / after lane L lies within
+// (16 L + 48) 1.02 u of it (16 L + 16 adds of the reference, 10 roundings of ours).  Then S is handed from lane to lane:
+// one exact add per lane, or the 16-step chain for the few lanes that straddle a binade (all lanes of a SLOW chunk).
+__device__ __noinline__ void exact_medium(const EncArgs& a, WarpBuf& sm, uint64_t cbase, uint64_t cend, float mn, bool submin,
+                                          bool slow, bool cbulk, int lane, float& total_out, float& ymx_out, float& y0_out) {
+  const float u24 = 1.0f / 16777216.0f;
+  const int cnt = (int)(cend - cbase);
+  const int nr = (cnt + DCB_WR - 1) / DCB_WR;
+  float S = 0.0f, ymx = __uint_as_float(0xff800000u), y0 = 0.0f;
+  warp_issue_x(a, cbase, cend, sm.X[0], lane, cbulk || round_is_bulk(a, cbase, cend));
+  cp_async_commit();
+  for (int j = 0; j < nr; j++) {
+    cp_async_wait<0>();
+    __syncwarp();
+    if (j + 1 < nr) warp_issue_x(a, cbase + (uint64_t)(j + 1) * DCB_WR, cend, sm.X[(j + 1) & 1], lane,
+                                 cbulk || round_is_bulk(a, cbase + (uint64_t)(j + 1) * DCB_WR, cend));
+    cp_async_commit();
+    const uint64_t my0 = cbase + (uint64_t)j * DCB_WR + (uint64_t)lane * DCB_E;
+    const int vcnt = (my0 >= cend) ? 0 : (int)min((uint64_t)DCB_E, cend - my0);
+    const float* slot = &sm.X[j & 1][lane * DCB_XPITCH];
+    float y[DCB_E];
+    #pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const float4 v = *reinterpret_cast<const float4*>(slot + 4 * q);
+      y[4 * q] = v.x; y[4 * q + 1] = v.y; y[4 * q + 2] = v.z; y[4 * q + 3] = v.w;
+    }
+    if (submin) {
+      #pragma unroll
+      for (int e = 0; e < DCB_E; e++) y[e] = (e < vcnt) ? __fsub_rn(y[e], mn) : 0.0f;   // + 0.0f leaves every sum as it is
+    }
+    if (j == 0) y0 = __shfl_sync(0xffffffffu, y[0], 0);
+    float d0 = -1.0f, d1 = -1.0f;                        // < 0: not a transducer
+    if (!slow) {
+      const float q0 = __fadd_rn(__fadd_rn(y[0], y[1]), __fadd_rn(y[2], y[3]));
+      const float q1 = __fadd_rn(__fadd_rn(y[4], y[5]), __fadd_rn(y[6], y[7]));
+      const float q2 = __fadd_rn(__fadd_rn(y[8], y[9]), __fadd_rn(y[10], y[11]));
+      const float q3 = __fadd_rn(__fadd_rn(y[12], y[13]), __fadd_rn(y[14], y[15]));
+      const float py = __fadd_rn(__fadd_rn(q0, q1), __fadd_rn(q2, q3));
+      float inc = py;
+      #pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const float t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc = __fadd_rn(inc, t);
+      }
+      const float before = __fadd_rn(S, __fsub_rn(inc, py)), after = __fadd_rn(S, inc);
+      const float r = (float)(16 * lane + 48) * (1.02f * u24);
+      const float lo = __fmul_rd(before, __fsub_rd(1.0f, r));
+      const float hi = __fmul_ru(__fmul_ru(after, __fadd_ru(1.0f, r)), 1.00001f);
+      const uint32_t elo = f2u(lo) >> 23, ehi = f2u(hi) >> 23;
+      if (elo == ehi && elo > 0u && elo < 255u) {
+        const float r0 = u2f(elo << 23), r1 = u2f((elo << 23) | 1u);
+        float c0 = r0, c1 = r1;
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) { c0 = __fadd_rn(c0, y[e]); c1 = __fadd_rn(c1, y[e]); }
+        d0 = __fsub_rn(c0, r0); d1 = __fsub_rn(c1, r1);  // exact: both ends lie on the grid of one binade
+      }
+    } else {
+      #pragma unroll
+      for (int e = 0; e < DCB_E; e++) if (e < vcnt) ymx = fmaxf(ymx, y[e]);
+    }
+    // S travels from lane to lane
+    float Sout = S;
+    for (int k = 0; k < 32; k++) {
+      const float Sin = (k == 0) ? S : __shfl_sync(0xffffffffu, Sout, k - 1);
+      if (lane == k) {
+        if (d0 >= 0.0f) {
+          Sout = __fadd_rn(Sin, (f2u(Sin) & 1u) ? d1 : d0);
+        } else {
+          float t = Sin;
+          #pragma unroll
+          for (int e = 0; e < DCB_E; e++) t = __fadd_rn(t, y[e]);
+          Sout = t;
+        }
+      }
+    }
+    S = __shfl_sync(0xffffffffu, Sout, 31);
+  }
+  if (slow) {
+    #pragma unroll
+    for (int o = 16; o; o >>= 1) ymx = fmaxf(ymx, __shfl_xor_sync(0xffffffffu, ymx, o));
+  }
+  __syncwarp();
+  total_out = S; ymx_out = ymx; y0_out = y0;
+}
+
+template <int CT>
+__global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_warp_kernel(const EncArgs a) {
+  extern __shared__ __align__(16) unsigned char dcb_warp_smem[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  WarpBuf& sm = reinterpret_cast<WarpBuf*>(dcb_warp_smem)[warp];
+  const uint32_t K = a.num_tiles;
+  const uint32_t nw = gridDim.x * (DCB_NT / 32);
+  uint32_t c = blockIdx.x * (DCB_NT / 32) + warp;
+  if (c >= K) return;
+
+  const bool submin = (a.flags & 1u) != 0;            // DCB_F_SUBTRACT_MIN
+  const bool fixed_mask = (a.flags & 2u) != 0;        // DCB_F_FIXED_MASK
+  const float u24 = 1.0f / 16777216.0f;
+  uint32_t* const W = sm.W;
+
+  Pass1 acc;
+  p1_reset<CT>(acc);
+  pass1_direct<CT>(a, (uint64_t)c * DCB_TILE, min((uint64_t)c * DCB_TILE + DCB_TILE, a.n), lane, acc, submin);
+
+  for (;;) {
+    const uint32_t cw = c;
+    const uint64_t cbase = (uint64_t)c * DCB_TILE;
+    const uint64_t cend = min(cbase + DCB_TILE, a.n);
+    const int cnt = (int)(cend - cbase);
+    const int nr = (cnt + DCB_WR - 1) / DCB_WR;
+    const bool cbulk = cnt == DCB_TILE && (a.flags & DCB_ENC_IN_ALIGNED);      // every round of this chunk is a bulk round
+    const bool fold_next = true;
+
+    // ---- statistics of this chunk (folded in during the previous chunk) ------------------------------------------
+    float lmn = acc.mn, lmx = acc.mx, tsum = __fadd_rn(acc.s0, acc.s1), wsum = acc.ws;
+    #pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      lmn = fminf(lmn, __shfl_xor_sync(0xffffffffu, lmn, o));
+      if (CT == CT_MASK) {
+        lmx = fmaxf(lmx, __shfl_xor_sync(0xffffffffu, lmx, o));
+        tsum = __fadd_rn(tsum, __shfl_xor_sync(0xffffffffu, tsum, o));
+        wsum = __fadd_rn(wsum, __shfl_xor_sync(0xffffffffu, wsum, o));
+      }
+    }
+    bool odd = !(fabsf(__fadd_rn(acc.n0, acc.n1)) < __uint_as_float(0x7f800000u));
+    if (!submin) odd = odd || ((acc.sg >> 31) != 0u);   // a negative value (sign bit, -0.0f included) without min-subtract
+    bool slow = __any_sync(0xffffffffu, odd);
+    float mn = submin ? lmn : 0.0f;
+    if (submin) {
+      if (mn == 0.0f) {
+        // +0 / -0 compare equal: the reference keeps the FIRST minimal element; recover its sign.  A -0.0f anywhere
+        // makes the chunk SLOW (x - (+0) keeps it negative and the raw code would carry its sign bit).
+        uint32_t fi = 0xFFFFFFFFu; bool negz = false;
+        for (int i = lane; i < cnt; i += 32) {
+          const float v = __ldg(a.in + cbase + i);
+          if (v == 0.0f && fi == 0xFFFFFFFFu) fi = (uint32_t)i;
+          negz = negz || (f2u(v) == 0x80000000u);
+        }
+        #pragma unroll
+        for (int o = 16; o; o >>= 1) fi = min(fi, __shfl_xor_sync(0xffffffffu, fi, o));
+        if (fi != 0xFFFFFFFFu) mn = __ldg(a.in + cbase + fi);
+        slow = slow || __any_sync(0xffffffffu, negz);
+      }
+      if (slow) {                                       // data[0] NaN: every '<' fails and min stays NaN (:3546-3553)
+        const float x0 = __ldg(a.in + cbase);
+        if (x0 != x0) mn = x0;
+      }
+      if (lane == 0) a.cmin[c] = mn;
+    } else if (a.cmin && lane == 0) {
+      a.cmin[c] = 0.0f;
+    }
+
+    // ---- med_dataset_float: only the top 17 bits of the sequential float32 mean reach the stream -----------------
+    int type = a.fixed_type;
+    uint32_t mask17 = a.fixed_mask17;
+    if (CT == CT_MASK && !fixed_mask) {
+      bool decided = false;
+      const float fc = (float)cnt;
+      if (!slow && !(a.flags & 8u)) {
+        // S_seq in est +- E (see dcb_encode_slots.cuh, LEVEL 0); the raw sum here is 2 + 16 + 1 + 5 roundings deep
+        const float amb = fmaxf(fabsf(lmn), fabsf(lmx));
+        float est = __fsub_rn(tsum, __fmul_rn(fc, mn));
+        // (ragged chunk / unaligned input: the per-lane sums are plain chains of up to 128 adds)
+        const float ke = cbulk ? 32.0f * u24 : 160.0f * u24;
+        float E1 = __fadd_ru(__fmul_ru(__fmul_ru(fc, amb), ke), 1e-37f);
+        if (submin && lmx == lmn) { est = 0.0f; E1 = 0.0f; }
+        const float top = fmaxf(__fadd_ru(est, E1), 0.0f);
+        float E = __fadd_ru(E1, __fmul_ru(__fmul_ru(__fadd_ru(fc, 4.0f), 1.01f * u24), top));
+        if (cbulk) {
+          // tighter: S_seq - sum y = sum_k delta_k with |delta_k| <= u (s_{k-1} + y_k) <= u (1 + gamma) P_k, P_k the exact partial
+          // sums, and sum_k P_k = sum_i (n - i) y_i <= (1 + u) (WX - min SW): WX = sum_i w_i x_i with w_i = n - (index of the
+          // first element of i's group of four) >= n - i, SW = sum_i w_i = n (n + 4) / 2.  wsum is WX to 40 roundings.
+          const float SW = 0.5f * (float)DCB_TILE * (float)(DCB_TILE + 4);                  // 8396800, exact
+          const float wup = fmaxf(__fadd_ru(__fsub_ru(wsum, __fmul_rn(mn, SW)), __fmul_ru(__fmul_ru(SW, amb), 48.0f * u24)), 0.0f);
+          const float E2 = __fadd_ru(E1, __fadd_ru(__fmul_ru(top, 4.0f * 1.01f * u24), __fmul_ru(wup, 1.002f * u24)));
+          E = fminf(E, E2);
+        }
+        const float flo = fmaxf(__fsub_rd(est, E), 0.0f), fhi = __fadd_ru(est, E);
+        uint32_t mlo, mhi;
+        if (cnt == DCB_TILE) { mlo = f2u(__fmul_rn(flo, 1.0f / 4096.0f)) >> 15; mhi = f2u(__fmul_rn(fhi, 1.0f / 4096.0f)) >> 15; }
+        else { mlo = f2u(__fdiv_rn(flo, fc)) >> 15; mhi = f2u(__fdiv_rn(fhi, fc)) >> 15; }
+        decided = (mlo == mhi) && (f2u(fhi) < 0x7F800000u);
+        if (decided) {
+          mask17 = mlo;
+          type = type_from_max(submin ? __fsub_rn(lmx, mn) : lmx);
+          if (lane == 0) { a.cmed[c] = u2f(mask17 << 15); a.ctype[c] = type; }
+        }
+      }
+      if (!decided) {
+        float total, ymx, y0;
+        exact_medium(a, sm, cbase, cend, mn, submin, slow, cbulk, lane, total, ymx, y0);
+        const float med = __fdiv_rn(total, fc);
+        type = slow ? ((y0 != y0) ? 0 : type_from_max(ymx)) : type_from_max(submin ? __fsub_rn(lmx, mn) : lmx);
+        mask17 = f2u(med) >> 15;
+        if (lane == 0) { a.cmed[c] = med; a.ctype[c] = type; }
+      }
+    }
+
+    // ---- the rounds ----------------------------------------------------------------------------------------------
+    const uint32_t cn = c + nw;
+    const bool has_next = fold_next && cn < K;
+    const uint64_t nbase = (uint64_t)cn * DCB_TILE;
+    const uint64_t nend = has_next ? min(nbase + DCB_TILE, a.n) : 0ull;
+    const int nrn = has_next ? (int)((nend - nbase + DCB_WR - 1) / DCB_WR) : 0;
+    const bool nbulk = has_next && (nend - nbase) == DCB_TILE && (a.flags & DCB_ENC_IN_ALIGNED);   // every round of the next chunk is a bulk round
+    if (fold_next) p1_reset<CT>(acc);
+    warp_issue_x(a, cbase, cend, sm.X[0], lane, cbulk || round_is_bulk(a, cbase, cend));
+    if (nrn > 0) warp_issue_p(a, nbase, sm.P, lane, nbulk || round_is_bulk(a, nbase, nend));
+    cp_async_commit();
+
+    uint32_t* const out32 = reinterpret_cast<uint32_t*>(a.slots + (uint64_t)cw * DCB_SLOT_PITCH);
+    uint32_t wbase = 0u, carry_bits = 0u, carry = 0u;  // words already in the slot, bits of the open word, the open word
+    float c1 = 0.0f, c2 = 0.0f, c3 = 0.0f;              // last three values of the previous round (after min-subtract)
+
+    for (int j = 0; j < nr; j++) {
+      cp_async_wait<0>();
+      __syncwarp();
+      if (j < nrn) warp_consume_p<CT>(a, nbase + (uint64_t)j * DCB_WR, nend, sm.P, lane, acc, submin,
+                                      nbulk || round_is_bulk(a, nbase + (uint64_t)j * DCB_WR, nend), j);
+      if (j + 1 < nr) warp_issue_x(a, cbase + (uint64_t)(j + 1) * DCB_WR, cend, sm.X[(j + 1) & 1], lane,
+                                   cbulk || round_is_bulk(a, cbase + (uint64_t)(j + 1) * DCB_WR, cend));
+      if (j + 1 < nrn) warp_issue_p(a, nbase + (uint64_t)(j + 1) * DCB_WR, sm.P, lane,
+                                    nbulk || round_is_bulk(a, nbase + (uint64_t)(j + 1) * DCB_WR, nend));
+      cp_async_commit();
+
+      const uint64_t my0 = cbase + (uint64_t)j * DCB_WR + (uint64_t)lane * DCB_E;
+      const int vcnt = (my0 >= cend) ? 0 : (int)min((uint64_t)DCB_E, cend - my0);
+      const bool first = (j == 0 && lane == 0);        // chunk start: elements 0..2 have no full history (:3330)
+      const float* slot = &sm.X[j & 1][lane * DCB_XPITCH];
+      float x[DCB_E];
+      #pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const float4 v = *reinterpret_cast<const float4*>(slot + 4 * q);
+        x[4 * q] = v.x; x[4 * q + 1] = v.y; x[4 * q + 2] = v.z; x[4 * q + 3] = v.w;
+      }
+      if (submin) {
+        if (cbase + (uint64_t)(j + 1) * DCB_WR <= cend) {   // warp-uniform: a full round
+          #pragma unroll
+          for (int e = 0; e < DCB_E; e++) x[e] = __fsub_rn(x[e], mn);
+        } else {
+          #pragma unroll
+          for (int e = 0; e < DCB_E; e++) x[e] = (e < vcnt) ? __fsub_rn(x[e], mn) : 0.0f;
+        }
+      }
+      float h1 = __shfl_up_sync(0xffffffffu, x[DCB_E - 1], 1);
+      float h2 = __shfl_up_sync(0xffffffffu, x[DCB_E - 2], 1);
+      float h3 = __shfl_up_sync(0xffffffffu, x[DCB_E - 3], 1);
+      if (lane == 0) { h1 = c1; h2 = c2; h3 = c3; }
+
+      // ---- classify ----------------------------------------------------------------------------------------------
+      uint32_t code[DCB_E];
+      int len[DCB_E];
+      uint32_t chi = 0u, clo = 0u;
+      uint32_t total = 0;
+      bool all3 = false;
+      if (!slow) {
+        if (CT != CT_NP) {
+          float b1 = h1, b2 = h2, b3 = h3;
+          float t1 = __fmul_rn(3.0f, b1), t2 = __fmul_rn(3.0f, b2);
+          #pragma unroll
+          for (int e = 0; e < DCB_E; e++) {
+            const float xe = x[e];
+            const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);                 // 2*b1 is exact: == __fmul_rn(2, b1)
+            const float p3 = __fadd_rn(__fsub_rn(t1, t2), b3);
+            const float d1 = fabsf(__fsub_rn(b1, xe));
+            const float d2 = fabsf(__fsub_rn(p2, xe));
+            const float d3 = fabsf(__fsub_rn(p3, xe));
+            const float dmin = fminf(fminf(d1, d2), d3);                       // no NaN/Inf here: plain min == the '<' chain
+            bool hit = dmin <= a.k.tp;                                         // diff_min <= absErrorBound, :3399
+            if (e < 3) hit = hit && !first;
+            const bool zero = xe <= a.k.tz;                                    // fabs(x) < absErrorBound (x >= 0), :3390
+            const uint32_t sel = (d1 == dmin) ? 5u : ((d2 == dmin) ? 6u : 7u);  // first minimum wins == strict '<' updates
+            const uint32_t f = zero ? 4u : (hit ? sel : 0u);
+            if (e <= 9) chi |= f << (29 - 3 * e);
+            else if (e == 10) { chi |= f >> 1; clo |= f << 31; }
+            else clo |= f << (61 - 3 * e);
+            b3 = b2; b2 = b1; b1 = xe;
+            t2 = t1; t1 = __fmul_rn(3.0f, xe);
+          }
+          all3 = (vcnt == DCB_E) && ((chi & 0x92492492u) == 0x92492492u) && ((clo & 0x49240000u) == 0x49240000u);
+        }
+        if (__all_sync(0xffffffffu, all3)) {
+          total = 48u;
+        } else {
+          all3 = false;
+          #pragma unroll
+          for (int e = 0; e < DCB_E; e++) {
+            const uint32_t f = (CT == CT_NP) ? 0u : C48_FIELD(chi, clo, e);
+            uint32_t ft; int fl;
+            fallback_top<CT, true>(f2u(x[e]), a.k, type, mask17, ft, fl);
+            code[e] = f ? (f << 29) : ft;
+            len[e] = f ? 3 : fl;
+            if (e >= vcnt) { code[e] = 0u; len[e] = 0; }
+            total += (uint32_t)len[e];
+          }
+        }
+      } else {
+        // -1.0f is the reference's "empty history slot" marker: rebuild the exact state this lane
+        // starts from by walking back over the chunk until three non-sentinel values are found.
+        float b3 = -1.0f, b2 = -1.0f, b1 = -1.0f;
+        if (vcnt > 0 && CT != CT_NP) {
+          float n0 = 0.0f, n1 = 0.0f, n2 = 0.0f;
+          int found = 0; bool last_sent = false;
+          for (uint64_t idx = my0; idx > cbase && found < 3; idx--) {
+            float v = __ldg(a.in + idx - 1);
+            if (submin) v = __fsub_rn(v, mn);
+            if (idx == my0) last_sent = (v == -1.0f);
+            if (v != -1.0f) {
+              if (found == 0) n0 = v; else if (found == 1) n1 = v; else n2 = v;
+              found++;
+            }
+          }
+          if (found == 1) { b3 = n0; }
+          else if (found == 2) { b3 = n1; b2 = n0; }
+          else if (found == 3) {
+            if (!last_sent) { b3 = n2; b2 = n1; b1 = n0; }
+            else { b3 = n1; b2 = n0; b1 = -1.0f; }
+          }
+        }
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) {
+          len[e] = 0; code[e] = 0u;
+          if (e < vcnt) classify_sentinel<CT>(x[e], b3, b2, b1, a.k, type, mask17, code[e], len[e]);
+          total += (uint32_t)len[e];
+        }
+      }
+      c1 = __shfl_sync(0xffffffffu, x[DCB_E - 1], 31);
+      c2 = __shfl_sync(0xffffffffu, x[DCB_E - 2], 31);
+      c3 = __shfl_sync(0xffffffffu, x[DCB_E - 3], 31);
+
+      // ---- warp scan of the bit counts; the round starts at bit carry_bits of the buffer -----------------------------
+      uint32_t incl = total;
+      #pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      const uint32_t R = carry_bits + __shfl_sync(0xffffffffu, incl, 31);       // bits in the buffer after this round
+      const uint32_t s = carry_bits + incl - total;                             // first bit of this lane
+      const unsigned havebits = __ballot_sync(0xffffffffu, total > 0u);
+      const bool fast_pack = __all_sync(0xffffffffu, total >= 32u || total == 0u);
+
+      // ---- pack ----------------------------------------------------------------------------------------------------
+      uint32_t hi = 0u;
+      const uint32_t f0 = s & 31u;
+      const uint32_t hw = s >> 5;
+      uint32_t newcarry;
+      if (fast_pack) {
+        uint32_t widx = hw;
+        if (all3) {
+          const uint32_t w0_ = chi >> f0;
+          const uint32_t w1_ = __funnelshift_r(clo, chi, f0);
+          const uint32_t w2_ = __funnelshift_r(0u, clo, f0);
+          W[hw] = w0_;
+          if (f0 >= 16u) { W[hw + 1] = w1_; hi = w2_; widx = hw + 2; }
+          else { hi = w1_; widx = hw + 1; }
+        } else {
+          uint32_t fill = f0;
+          #pragma unroll
+          for (int e = 0; e < DCB_E; e++) {
+            const uint32_t cl = code[e];
+            hi |= cl >> fill;
+            const uint32_t lo = __funnelshift_r(0u, cl, fill);
+            fill += (uint32_t)len[e];
+            const bool fl = fill >= 32u;
+            if (fl) W[widx] = hi;
+            widx += fl ? 1u : 0u;
+            hi = fl ? lo : hi;
+            fill &= 31u;
+          }
+        }
+        // the word straddling two lanes is stored by the later one; it ORs in the earlier lane's tail (lane 0: the carry)
+        uint32_t prevT = __shfl_up_sync(0xffffffffu, hi, 1);
+        if (lane == 0) prevT = carry;
+        if (total > 0u && f0) W[hw] |= prevT;
+        const int lastl = 31 - __clz((int)havebits);                            // last lane that has bits (a round has >= 1 element)
+        newcarry = __shfl_sync(0xffffffffu, hi, lastl);
+        __syncwarp();
+      } else {
+        // ragged round (a lane with fewer than 11 valid elements): zero the buffer and OR every word in
+        for (int i = lane; i < DCB_WWORDS; i += 32) W[i] = 0u;
+        __syncwarp();
+        if (lane == 0 && carry_bits) atomicOr(&W[0], carry);
+        uint32_t fill = f0, widx = hw;
+        if (all3) {
+          #pragma unroll
+          for (int e = 0; e < DCB_E; e++) { code[e] = C48_FIELD(chi, clo, e) << 29; len[e] = 3; }
+        }
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) {
+          const uint32_t L = (uint32_t)len[e];
+          if (L) {
+            const uint32_t cl = code[e];
+            hi |= cl >> fill;
+            const uint32_t lo = __funnelshift_r(0u, cl, fill);
+            fill += L;
+            if (fill >= 32u) { atomicOr(&W[widx++], hi); hi = lo; fill -= 32u; }
+          }
+        }
+        if (fill && total > 0u) atomicOr(&W[widx], hi);
+        __syncwarp();
+        newcarry = W[R >> 5];
+      }
+
+      // ---- whole words leave for the slot ----------------------------------------------------------------------------
+      const uint32_t fullw = R >> 5;
+      {
+        uint32_t* const o = out32 + wbase;                                      // a round of 3-bit codes is 48 or 49 words
+        if ((uint32_t)lane < fullw) o[lane] = __byte_perm(W[lane], 0u, 0x0123);
+        if ((uint32_t)lane + 32u < fullw) o[lane + 32] = __byte_perm(W[lane + 32], 0u, 0x0123);
+        if (fullw > 64u)
+          for (uint32_t k = (uint32_t)lane + 64u; k < fullw; k += 32u) o[k] = __byte_perm(W[k], 0u, 0x0123);
+      }
+      wbase += fullw;
+      carry_bits = R & 31u;
+      carry = carry_bits ? newcarry : 0u;
+    }
+
+    // ---- chunk end: the open word (zero padded, :5467), the size ----------------------------------------------------
+    if (lane == 0) {
+      if (carry_bits) out32[wbase] = __byte_perm(carry, 0u, 0x0123);
+      const uint32_t bits = wbase * 32u + carry_bits;
+      const uint32_t bytes = (bits + 7u) >> 3;
+      a.sizes[cw] = bytes;
+      atomicAdd(&a.gsum[cw / DCB_GROUP], bytes);
+      if (cw == K - 1u) *a.last_tile_bits = bits;
+    }
+    if (!has_next) break;
+    c = cn;
+  }
+}

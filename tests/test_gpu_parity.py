@@ -292,3 +292,46 @@ def test_full_size_properties(ct, kind, dev):
     torch.cuda.synchronize()
     assert comp2.total_bytes() == tot1 and torch.equal(comp2.chunk_crc[:K], crc1)
     assert torch.equal(comp2.chunk_offsets[:K + 1], offs)
+
+
+@pytest.mark.parametrize("ct", CTS)
+def test_one_tile_chunks_ragged_unaligned(ct, dev):
+    """One chunk == one tile (the slot path: dcb_encode_warp / dcb_encode_slots + dcb_compact): a ragged last chunk, an input
+    pointer that is only 4-byte aligned, sizes around the group size of the compaction kernel (64 chunks)."""
+    rng = np.random.default_rng(11 + ct)
+    for n in (4096 * 3 + 17, 4096 * 64, 4096 * 65 + 511, 4096 * 130 + 2049):
+        x = np.concatenate([make_field("smooth", n // 2), make_field("noisy", n - n // 2)]).astype(np.float32)
+        x[rng.integers(0, n, 50)] = 0.0
+        assert_same_as_oracle(x, ct, 0.01, 4096, dev, tag="ragged n=%d ct=%d" % (n, ct))
+    # unaligned device pointer: a view that starts one float into the allocation
+    n = 4096 * 9 + 100
+    base = torch.from_numpy(np.concatenate([[0.0], make_field("noisy", n)]).astype(np.float32)).to(dev)
+    xd = base[1:]
+    assert xd.data_ptr() % 16 == 4
+    comp = api.compress(xd, ct=ct, abs_error_bound=1e-4, chunk_elems=4096, crc=True)
+    torch.cuda.synchronize()
+    x = xd.cpu().numpy()
+    enc = ol.o_compress_chunked(ct, x, 4096, 1e-4, want_crc=True)
+    total = comp.total_bytes()
+    assert total == enc["stream"].size
+    assert np.array_equal(comp.stream[:total].cpu().numpy(), enc["stream"])
+    d = api.decompress(comp).cpu().numpy()
+    od = ol.o_decompress_chunked(ct, enc, n, 4096, 1e-4)
+    assert np.array_equal(d.view(np.uint32), od.view(np.uint32))
+
+
+@pytest.mark.parametrize("encoder", ("warp", "slots", "single"))
+def test_every_encoder_kernel(encoder):
+    """The library picks one of three encoders for one-tile chunks (dcb_abi.cu encoder_choice).  DCB_ENCODER forces one for
+    every CT; it is read once per process, so the parity tests of this module are rerun in a child process."""
+    import subprocess
+    import sys
+    if os.environ.get("DCB_ENCODER"):
+        pytest.skip("already inside a forced-encoder run")
+    env = dict(os.environ, DCB_ENCODER=encoder)
+    here = os.path.abspath(__file__)
+    sel = "test_fields_chunked or test_no_min_subtract_and_fixed_mask or test_encoder_only_inputs or " \
+          "test_exact_medium_transducer_sum or test_golden_fixtures or test_one_tile_chunks_ragged_unaligned"
+    r = subprocess.run([sys.executable, "-m", "pytest", here, "-x", "-q", "-m", "gpu", "-k", sel, "-p", "no:cacheprovider"],
+                       env=env, capture_output=True, text=True, cwd=os.path.dirname(os.path.dirname(here)))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]

@@ -1,7 +1,7 @@
 #!/bin/bash
 # A/B on the GPU box: parity tests, then encode/decode times for CT x field (device resident, no CPU baseline)
 python -m pytest tests -m gpu -x -q 2>&1 | tail -8
-for f in smooth noisy constant; do for ct in 5 7; do
+for f in smooth noisy constant; do for ct in ${CTS:-5 7}; do
   python bench.py --ct $ct --field $f --steps 10 --warmup 3 --no-cpu --no-e2e 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.read()); c=d['config']
