@@ -54,6 +54,36 @@ __device__ __forceinline__ void copy_out_slot(uint8_t* slot, const uint32_t* W, 
   }
 }
 
+// One element of the FAST classification.  The 3-bit field (preset to 100 = "zero") is raised to 101 / 110 / 111 by up to
+// three predicated multiply-adds, a miss sets the element's bit in `miss`.  Written in PTX so that the compares chain
+// through predicates (FSETP ... .AND P) and the field updates are IMADs: the ALU pipe (FSETP, SEL, FMNMX, LOP3) is the busy
+// one in this kernel, the FMA pipe (FADD, FMUL, IMAD) has room (profiles/r1_summary.md) -- 6 ALU-pipe instructions per
+// element instead of 10.  zero: x <= tz; hit: min |e_i| <= tp; the FIRST minimum wins (strict '<' updates, :3373).
+template <uint32_t FIELD_ONE>
+__device__ __forceinline__ void classify_pred(uint32_t& fields, uint32_t& miss, float xe, float e1, float e2, float e3,
+                                              float tz, float tp, uint32_t one, uint32_t miss_bit) {
+  asm("{\n\t"
+      ".reg .pred pnz, ph, pa, pb, pm;\n\t"
+      ".reg .f32 a1, a2, a3, dm;\n\t"
+      "abs.f32 a1, %3;\n\t"
+      "abs.f32 a2, %4;\n\t"
+      "abs.f32 a3, %5;\n\t"
+      "min.f32 dm, a1, a2;\n\t"
+      "min.f32 dm, dm, a3;\n\t"
+      "setp.gt.f32 pnz, %2, %6;\n\t"
+      "setp.le.and.f32 ph, dm, %7, pnz;\n\t"
+      "setp.gt.and.f32 pm, dm, %7, pnz;\n\t"
+      "setp.neu.and.f32 pa, a1, dm, ph;\n\t"
+      "setp.neu.and.f32 pb, a2, dm, pa;\n\t"
+      "@ph mad.lo.u32 %0, %8, %9, %0;\n\t"
+      "@pa mad.lo.u32 %0, %8, %9, %0;\n\t"
+      "@pb mad.lo.u32 %0, %8, %9, %0;\n\t"
+      "@pm mad.lo.u32 %1, %8, %10, %1;\n\t"
+      "}"
+      : "+r"(fields), "+r"(miss)
+      : "f"(xe), "f"(e1), "f"(e2), "f"(e3), "f"(tz), "f"(tp), "r"(one), "n"(FIELD_ONE), "r"(miss_bit));
+}
+
 template <int CT>
 __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slots_kernel(const EncArgs a) {
   extern __shared__ __align__(16) unsigned char dcb_slot_smem[];
@@ -67,6 +97,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
 
   const bool submin = (a.flags & 1u) != 0;            // DCB_F_SUBTRACT_MIN
   const bool fixed_mask = (a.flags & 2u) != 0;        // DCB_F_FIXED_MASK
+  const uint32_t one = (a.flags >> 31) + 1u;          // 1, but opaque to the compiler (keeps the field updates on IMAD)
 
   uint32_t fix_hw = 0; bool fix_need = false;         // lane 0 of warps > 0: first word of the pending tile still lacks the previous warp's tail
   uint32_t pend_tile = 0u, pend_bits = 0u;            // tile packed in the previous iteration (copied out in this one)
@@ -400,30 +431,28 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
     uint32_t total = 0;
     bool all3 = false;
     if (!slow) {
+      uint32_t miss = 0u;                              // bit e: element e needs a fallback code
       if (CT != CT_NP) {
         float b1 = h1, b2 = h2, b3 = h3;
         float t1 = __fmul_rn(3.0f, b1), t2 = __fmul_rn(3.0f, b2);
-        #pragma unroll
-        for (int e = 0; e < DCB_E; e++) {
-          const float xe = x[e];
-          const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);
-          const float p3 = __fadd_rn(__fsub_rn(t1, t2), b3);
-          const float d1 = fabsf(__fsub_rn(b1, xe));
-          const float d2 = fabsf(__fsub_rn(p2, xe));
-          const float d3 = fabsf(__fsub_rn(p3, xe));
-          const float dmin = fminf(fminf(d1, d2), d3);
-          bool hit = dmin <= a.k.tp;
-          if (e < 3) hit = hit && !first;
-          const bool zero = xe <= a.k.tz;
-          const uint32_t sel = (d1 == dmin) ? 5u : ((d2 == dmin) ? 6u : 7u);
-          const uint32_t f = zero ? 4u : (hit ? sel : 0u);
-          if (e <= 9) chi |= f << (29 - 3 * e);
-          else if (e == 10) { chi |= f >> 1; clo |= f << 31; }
-          else clo |= f << (61 - 3 * e);
-          b3 = b2; b2 = b1; b1 = xe;
-          t2 = t1; t1 = __fmul_rn(3.0f, xe);
-        }
-        all3 = (vcnt == DCB_E) && ((chi & 0x92492492u) == 0x92492492u) && ((clo & 0x49240000u) == 0x49240000u);
+        uint32_t fa = 0x92492490u, fb = 0x92490000u;   // 3-bit fields of elements 0..9 / 10..15, all preset to 100 (zero)
+        const float tp3 = first ? -1.0f : a.k.tp;      // chunk start: elements 0..2 never hit
+        #define DCB_CLS(E, ACC, POS, TP) do {                                                                   \
+            const float xe = x[E];                                                                               \
+            const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);             /* 2*b1 is exact */                   \
+            const float p3 = __fadd_rn(__fsub_rn(t1, t2), b3);                                                   \
+            classify_pred<(1u << (POS))>(ACC, miss, xe, __fsub_rn(b1, xe), __fsub_rn(p2, xe), __fsub_rn(p3, xe), \
+                                         a.k.tz, TP, one, 1u << (E));                                            \
+            b3 = b2; b2 = b1; b1 = xe; t2 = t1; t1 = __fmul_rn(3.0f, xe);                                        \
+          } while (0)
+        DCB_CLS(0, fa, 29, tp3); DCB_CLS(1, fa, 26, tp3); DCB_CLS(2, fa, 23, tp3); DCB_CLS(3, fa, 20, a.k.tp);
+        DCB_CLS(4, fa, 17, a.k.tp); DCB_CLS(5, fa, 14, a.k.tp); DCB_CLS(6, fa, 11, a.k.tp); DCB_CLS(7, fa, 8, a.k.tp);
+        DCB_CLS(8, fa, 5, a.k.tp); DCB_CLS(9, fa, 2, a.k.tp);
+        DCB_CLS(10, fb, 29, a.k.tp); DCB_CLS(11, fb, 26, a.k.tp); DCB_CLS(12, fb, 23, a.k.tp); DCB_CLS(13, fb, 20, a.k.tp);
+        DCB_CLS(14, fb, 17, a.k.tp); DCB_CLS(15, fb, 14, a.k.tp);
+        #undef DCB_CLS
+        chi = fa | (fb >> 30); clo = fb << 2;          // the 48-bit string: 30 bits of fa, 18 bits of fb
+        all3 = (vcnt == DCB_E) && (miss == 0u);
       }
       if (__all_sync(0xffffffffu, all3)) {
         total = 48u;
@@ -431,7 +460,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
         all3 = false;
         #pragma unroll
         for (int e = 0; e < DCB_E; e++) {
-          const uint32_t f = (CT == CT_NP) ? 0u : C48_FIELD(chi, clo, e);
+          const uint32_t f = (CT == CT_NP || ((miss >> e) & 1u)) ? 0u : C48_FIELD(chi, clo, e);
           uint32_t ft; int fl;
           fallback_top<CT, true>(f2u(x[e]), a.k, type, mask17, ft, fl);
           code[e] = f ? (f << 29) : ft;

@@ -228,6 +228,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_war
   const bool fixed_mask = (a.flags & 2u) != 0;        // DCB_F_FIXED_MASK
   const float u24 = 1.0f / 16777216.0f;
   uint32_t* const W = sm.W;
+  const uint32_t one = (a.flags >> 31) + 1u;          // 1, but opaque to the compiler (keeps the field updates on IMAD)
 
   Pass1 acc;
   p1_reset<CT>(acc);
@@ -385,30 +386,28 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_war
       uint32_t total = 0;
       bool all3 = false;
       if (!slow) {
+        uint32_t miss = 0u;                              // bit e: element e needs a fallback code
         if (CT != CT_NP) {
           float b1 = h1, b2 = h2, b3 = h3;
           float t1 = __fmul_rn(3.0f, b1), t2 = __fmul_rn(3.0f, b2);
-          #pragma unroll
-          for (int e = 0; e < DCB_E; e++) {
-            const float xe = x[e];
-            const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);                 // 2*b1 is exact: == __fmul_rn(2, b1)
-            const float p3 = __fadd_rn(__fsub_rn(t1, t2), b3);
-            const float d1 = fabsf(__fsub_rn(b1, xe));
-            const float d2 = fabsf(__fsub_rn(p2, xe));
-            const float d3 = fabsf(__fsub_rn(p3, xe));
-            const float dmin = fminf(fminf(d1, d2), d3);                       // no NaN/Inf here: plain min == the '<' chain
-            bool hit = dmin <= a.k.tp;                                         // diff_min <= absErrorBound, :3399
-            if (e < 3) hit = hit && !first;
-            const bool zero = xe <= a.k.tz;                                    // fabs(x) < absErrorBound (x >= 0), :3390
-            const uint32_t sel = (d1 == dmin) ? 5u : ((d2 == dmin) ? 6u : 7u);  // first minimum wins == strict '<' updates
-            const uint32_t f = zero ? 4u : (hit ? sel : 0u);
-            if (e <= 9) chi |= f << (29 - 3 * e);
-            else if (e == 10) { chi |= f >> 1; clo |= f << 31; }
-            else clo |= f << (61 - 3 * e);
-            b3 = b2; b2 = b1; b1 = xe;
-            t2 = t1; t1 = __fmul_rn(3.0f, xe);
-          }
-          all3 = (vcnt == DCB_E) && ((chi & 0x92492492u) == 0x92492492u) && ((clo & 0x49240000u) == 0x49240000u);
+          uint32_t fa = 0x92492490u, fb = 0x92490000u;   // 3-bit fields of elements 0..9 / 10..15, all preset to 100 (zero)
+          const float tp3 = first ? -1.0f : a.k.tp;      // chunk start: elements 0..2 never hit
+          #define DCB_CLS(E, ACC, POS, TP) do {                                                                   \
+              const float xe = x[E];                                                                               \
+              const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);             /* 2*b1 is exact */                   \
+              const float p3 = __fadd_rn(__fsub_rn(t1, t2), b3);                                                   \
+              classify_pred<(1u << (POS))>(ACC, miss, xe, __fsub_rn(b1, xe), __fsub_rn(p2, xe), __fsub_rn(p3, xe), \
+                                           a.k.tz, TP, one, 1u << (E));                                            \
+              b3 = b2; b2 = b1; b1 = xe; t2 = t1; t1 = __fmul_rn(3.0f, xe);                                        \
+            } while (0)
+          DCB_CLS(0, fa, 29, tp3); DCB_CLS(1, fa, 26, tp3); DCB_CLS(2, fa, 23, tp3); DCB_CLS(3, fa, 20, a.k.tp);
+          DCB_CLS(4, fa, 17, a.k.tp); DCB_CLS(5, fa, 14, a.k.tp); DCB_CLS(6, fa, 11, a.k.tp); DCB_CLS(7, fa, 8, a.k.tp);
+          DCB_CLS(8, fa, 5, a.k.tp); DCB_CLS(9, fa, 2, a.k.tp);
+          DCB_CLS(10, fb, 29, a.k.tp); DCB_CLS(11, fb, 26, a.k.tp); DCB_CLS(12, fb, 23, a.k.tp); DCB_CLS(13, fb, 20, a.k.tp);
+          DCB_CLS(14, fb, 17, a.k.tp); DCB_CLS(15, fb, 14, a.k.tp);
+          #undef DCB_CLS
+          chi = fa | (fb >> 30); clo = fb << 2;          // the 48-bit string: 30 bits of fa, 18 bits of fb
+          all3 = (vcnt == DCB_E) && (miss == 0u);
         }
         if (__all_sync(0xffffffffu, all3)) {
           total = 48u;
@@ -416,7 +415,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_war
           all3 = false;
           #pragma unroll
           for (int e = 0; e < DCB_E; e++) {
-            const uint32_t f = (CT == CT_NP) ? 0u : C48_FIELD(chi, clo, e);
+            const uint32_t f = (CT == CT_NP || ((miss >> e) & 1u)) ? 0u : C48_FIELD(chi, clo, e);
             uint32_t ft; int fl;
             fallback_top<CT, true>(f2u(x[e]), a.k, type, mask17, ft, fl);
             code[e] = f ? (f << 29) : ft;
