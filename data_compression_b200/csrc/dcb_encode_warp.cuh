@@ -385,6 +385,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_war
       uint32_t chi = 0u, clo = 0u;
       uint32_t total = 0;
       bool all3 = false;
+      int np = DCB_E;                                  // pieces the packing loop has to place (warp-uniform)
       if (!slow) {
         uint32_t miss = 0u;                              // bit e: element e needs a fallback code
         if (CT != CT_NP) {
@@ -409,8 +410,31 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_war
           chi = fa | (fb >> 30); clo = fb << 2;          // the 48-bit string: 30 bits of fa, 18 bits of fb
           all3 = (vcnt == DCB_E) && (miss == 0u);
         }
-        if (__all_sync(0xffffffffu, all3)) {
+        // The first three elements of a chunk never hit (:3330), so the chunk's first lane always needs fallback codes: when that
+        // is the only reason the warp is not pure 3-bit codes, only that lane leaves the fast path, with five pieces to pack
+        // (three codes, then its remaining thirteen 3-bit codes as 32 + 7 bits) instead of sixteen.
+        const bool warp_all3 = __all_sync(0xffffffffu, all3);
+        const bool head_ok = all3 || (CT != CT_NP && first && vcnt == DCB_E && (miss & ~7u) == 0u);
+        const bool headcase = !warp_all3 && __all_sync(0xffffffffu, head_ok);
+        if (warp_all3) {
           total = 48u;
+        } else if (headcase) {
+          np = 5;
+          if (all3) {
+            total = 48u;
+          } else {
+            #pragma unroll
+            for (int e = 0; e < 3; e++) {
+              const uint32_t f = ((miss >> e) & 1u) ? 0u : C48_FIELD(chi, clo, e);
+              uint32_t ft; int fl;
+              fallback_top<CT, true>(f2u(x[e]), a.k, type, mask17, ft, fl);
+              code[e] = f ? (f << 29) : ft;
+              len[e] = f ? 3 : fl;
+            }
+            code[3] = (chi << 9) | (clo >> 23); len[3] = 32;
+            code[4] = clo << 9; len[4] = 7;
+            total = (uint32_t)(len[0] + len[1] + len[2]) + 39u;
+          }
         } else {
           all3 = false;
           #pragma unroll
@@ -488,6 +512,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_war
           uint32_t fill = f0;
           #pragma unroll
           for (int e = 0; e < DCB_E; e++) {
+            if (e >= np) break;
             const uint32_t cl = code[e];
             hi |= cl >> fill;
             const uint32_t lo = __funnelshift_r(0u, cl, fill);
@@ -518,6 +543,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_war
         }
         #pragma unroll
         for (int e = 0; e < DCB_E; e++) {
+          if (e >= np) break;
           const uint32_t L = (uint32_t)len[e];
           if (L) {
             const uint32_t cl = code[e];
