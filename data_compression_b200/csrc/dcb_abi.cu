@@ -235,6 +235,9 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
   a.last_bits = (unsigned long long*)((char*)d_ws + 8);
   a.status = (unsigned long long*)((char*)d_ws + 256);
   if (((uintptr_t)d_in & 15) == 0) a.flags |= DCB_ENC_IN_ALIGNED;
+#ifdef DCB_DEBUG_MED
+  if (const char* dm = getenv("DCB_DEBUG_MED")) a.flags |= (uint32_t)atoi(dm) << 16;
+#endif
 
   // a chunk is "one tile" when every chunk fits a single thread block: min / medium are fused in the encoder
   const bool is_tile = chunk_is_tile(n, chunk);
@@ -721,6 +724,14 @@ extern "C" int dcb_decompress_host(int ct, const uint8_t* h_stream, const uint64
 extern "C" int dcb_debug_timeline(long long* host_dst) {
   CK(cudaDeviceSynchronize());
   CK(cudaMemcpyFromSymbol(host_dst, g_dbg_ts, sizeof(g_dbg_ts)));
+  return DCB_OK;
+}
+#endif
+
+#ifdef DCB_DEBUG_MED
+extern "C" int dcb_debug_walk(unsigned long long* host_dst) {
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpyFromSymbol(host_dst, g_dbg_walk, sizeof(g_dbg_walk)));
   return DCB_OK;
 }
 #endif

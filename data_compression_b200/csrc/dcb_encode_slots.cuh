@@ -22,6 +22,9 @@
 #define DCB_GROUP 64u              // chunks per compaction block
 #define DCB_SLOT_BLOCKS_PER_SM 3
 
+#ifdef DCB_DEBUG_MED
+__device__ unsigned long long g_dbg_walk[8];   // cycles: whole level 2, serial loop; counts; stops
+#endif
 struct SlotSmem {
   float X[2][DCB_NT * DCB_XPITCH];   // double-buffered input tiles, one 80-byte slot per thread
   uint32_t W[2][DCB_TILE + 8];       // packed tiles (double buffered): stream word k of the tile lives at W[b][k]
@@ -39,6 +42,7 @@ struct SlotSmem {
   float mn, med;
   int type;
   uint32_t fi;
+  uint32_t tkt[2];                   // tile tickets: prologue pair, then the ticket of the tile after next (by parity)
 };
 
 // packed tile -> its scratch slot: MSB-first byte order, aligned 128-bit stores, no shift (a slot starts a chunk)
@@ -89,9 +93,13 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
   extern __shared__ __align__(16) unsigned char dcb_slot_smem[];
   SlotSmem& sm = *reinterpret_cast<SlotSmem*>(dcb_slot_smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  uint32_t cur = blockIdx.x;
+  // Tiles are handed out by a ticket counter: their cost differs by 2x (CT=7: a chunk whose mask needs the exact walk, a
+  // noisy chunk next to a constant one), and with a static stride the periodic bench field put every expensive chunk on a
+  // quarter of the blocks (444 = 12 mod 16).  No block ever waits for another one, so a ticket is only load balancing.
+  if (tid == 0) { sm.tkt[0] = atomicAdd(a.ticket, 1u); sm.tkt[1] = atomicAdd(a.ticket, 1u); }
+  __syncthreads();
+  uint32_t cur = sm.tkt[0], nxt = sm.tkt[1];
   if (cur >= a.num_tiles) return;
-  const uint32_t stride = gridDim.x;
   issue_tile_load(a, cur, sm.X[0], tid);
   cp_async_commit();
 
@@ -107,9 +115,10 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
   for (;; it++) {
     const int buf = (int)(it & 1u);
     float* slot = &sm.X[buf][tid * DCB_XPITCH];
-    const uint32_t nxt = cur + stride;
     if (nxt < a.num_tiles) issue_tile_load(a, nxt, sm.X[buf ^ 1], tid);
     cp_async_commit();
+    uint32_t tk = 0u;
+    if (tid == DCB_TKT_TID) tk = atomicAdd(a.ticket, 1u);               // ticket of the tile after next (lands during this tile)
     uint32_t* const W = sm.W[buf];
 
     const uint32_t tile = cur, c = cur;
@@ -276,6 +285,9 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
         if (full) { mlo = f2u(__fmul_rn(flo, 1.0f / 4096.0f)) >> 15; mhi = f2u(__fmul_rn(fhi, 1.0f / 4096.0f)) >> 15; }   // == division
         else { mlo = f2u(__fdiv_rn(flo, fc)) >> 15; mhi = f2u(__fdiv_rn(fhi, fc)) >> 15; }
         decided = (mlo == mhi) && (f2u(fhi) < 0x7F800000u);
+#ifdef DCB_DEBUG_MED
+        if (a.flags & (1u << 17)) decided = true;
+#endif
         if (decided) {
           mask17 = mlo;
           type = type_from_max(submin ? __fsub_rn(lmx, mn) : lmx);
@@ -334,6 +346,9 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
             if (full) { mlo = f2u(__fmul_rn(blo, 1.0f / 4096.0f)) >> 15; mhi = f2u(__fmul_rn(bhi, 1.0f / 4096.0f)) >> 15; }
             else { mlo = f2u(__fdiv_rn(blo, fc)) >> 15; mhi = f2u(__fdiv_rn(bhi, fc)) >> 15; }
             decided = (mlo == mhi) && (f2u(bhi) < 0x7F800000u);
+#ifdef DCB_DEBUG_MED
+            if (a.flags & (1u << 16)) decided = true;
+#endif
             if (decided) {
               mask17 = mlo;
               type = type_from_max(submin ? __fsub_rn(lmx, mn) : lmx);
@@ -355,29 +370,48 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
             __syncthreads();
             if (lane == 0) sm.red_mx[par][warp] = ymx;
           }
-          {
-            const bool certain = d0 >= 0.0f;
-            const unsigned cm = __ballot_sync(0xffffffffu, certain);
-            const uint32_t ebits = certain ? (f2u(lo_keep) >> 23) : 0u;
-            const uint32_t eprev = __shfl_up_sync(0xffffffffu, ebits, 1);
-            const bool head = certain && (lane == 0 || !((cm >> (lane - 1)) & 1u) || eprev != ebits);
-            const unsigned hm = __ballot_sync(0xffffffffu, head);
-            const int rs = 31 - __clz((int)(hm & (0xFFFFFFFFu >> (31 - lane))));
-            const float r0 = u2f(ebits << 23);
-            #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-              const float e0 = __shfl_up_sync(0xffffffffu, d0, o), e1 = __shfl_up_sync(0xffffffffu, d1, o);
-              if (certain && lane - o >= rs) {
-                const bool q0 = (f2u(__fadd_rn(r0, e0)) & 1u) != 0u, q1 = (f2u(__fadd_rn(r0, e1)) & 1u) != 0u;
-                const float n0 = __fadd_rn(e0, q0 ? d1 : d0), n1 = __fadd_rn(e1, q1 ? d0 : d1);
-                d0 = n0; d1 = n1;
-              }
+#ifdef DCB_DEBUG_MED
+          const long long dbg_l2_t0 = clock64();
+#endif
+          // Runs of consecutive transducer threads in the same binade compose (associatively) into one transducer:
+          // segmented warp scan.  (E then O)_p = E_p + O_{p ^ parity(E_p / q)}; every sum is exact (< 2^e, on the grid).
+          const bool certain = d0 >= 0.0f;
+          const unsigned cm = __ballot_sync(0xffffffffu, certain);
+          const uint32_t ebits = certain ? (f2u(lo_keep) >> 23) : 0u;
+          const uint32_t eprev = __shfl_up_sync(0xffffffffu, ebits, 1);
+          const bool head = certain && (lane == 0 || !((cm >> (lane - 1)) & 1u) || eprev != ebits);
+          const unsigned hm = __ballot_sync(0xffffffffu, head);
+          const int rs = 31 - __clz((int)(hm & (0xFFFFFFFFu >> (31 - lane))));
+          const float r0 = u2f(ebits << 23);
+          #pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const float e0 = __shfl_up_sync(0xffffffffu, d0, o), e1 = __shfl_up_sync(0xffffffffu, d1, o);
+            if (certain && lane - o >= rs) {
+              const bool q0 = (f2u(__fadd_rn(r0, e0)) & 1u) != 0u, q1 = (f2u(__fadd_rn(r0, e1)) & 1u) != 0u;
+              const float n0 = __fadd_rn(e0, q0 ? d1 : d0), n1 = __fadd_rn(e1, q1 ? d0 : d1);
+              d0 = n0; d1 = n1;
             }
-            const bool tail = certain && (lane == 31 || ((hm >> (lane + 1)) & 1u) || !((cm >> (lane + 1)) & 1u));
-            const unsigned wp = __ballot_sync(0xffffffffu, !certain || tail);
-            if (lane == 0) sm.walkmask[warp] = wp;
           }
-          slot[16] = d0; slot[17] = d1;
+          const bool tail = certain && (lane == 31 || ((hm >> (lane + 1)) & 1u) || !((cm >> (lane + 1)) & 1u));
+          const bool stop = !certain || tail;             // where the sequential walk has to stop
+          const unsigned wp = __ballot_sync(0xffffffffu, stop);
+          if (lane == 0) sm.walkmask[warp] = wp;
+          __syncthreads();
+          // The stops are compacted into one list (run transducers, or "chain thread t" markers) so that the one
+          // sequential pass reads consecutive entries: the walker's dependent chain is parity -> select -> add and nothing
+          // else (a walk that looked up masks, thread ids and slots on the way took 15 us per tile, profiles/r1_summary.md).
+          float2* const stopv = reinterpret_cast<float2*>(sm.W[buf]);      // free until this tile is packed
+          uint32_t before = 0u, ns = 0u;
+          #pragma unroll
+          for (int w = 0; w < DCB_NT / 32; w++) {
+            const uint32_t pc = (uint32_t)__popc(sm.walkmask[w]);
+            if (w < warp) before += pc;
+            ns += pc;
+          }
+          if (stop) {
+            const uint32_t rank = before + (uint32_t)__popc(wp & ((1u << lane) - 1u));
+            stopv[rank] = certain ? make_float2(d0, d1) : make_float2(-1.0f, __int_as_float(tid));
+          }
           __syncthreads();
           if (tid == 0) {
             float mx = submin ? __fsub_rn(lmx, mn) : lmx;
@@ -388,30 +422,28 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
             }
             float total = 0.0f;
             const float* Y = sm.X[buf];
-            int w = 0;
-            unsigned m = sm.walkmask[0];
-            int t = -1;
-            float2 d = make_float2(0.0f, 0.0f);
-            #define DCB_NEXT_STOP(T_, D_) do {                                                             \
-                while (m == 0u && w + 1 < DCB_NT / 32) m = sm.walkmask[++w];                                \
-                if (m) { T_ = w * 32 + (__ffs((int)m) - 1); m &= m - 1u;                                    \
-                         D_ = *reinterpret_cast<const float2*>(Y + T_ * DCB_XPITCH + 16); }                 \
-                else T_ = -1;                                                                               \
-              } while (0)
-            DCB_NEXT_STOP(t, d);
-            while (t >= 0) {
-              int tn; float2 dn = make_float2(0.0f, 0.0f);
-              DCB_NEXT_STOP(tn, dn);
+#ifdef DCB_DEBUG_MED
+            const long long dbg_w_t0 = clock64();
+#endif
+            float2 d = stopv[0];
+            for (uint32_t k = 0; k < ns; k++) {
+              const float2 dn = stopv[k + 1u];             // (one entry past the end is still inside the buffer)
               if (d.x >= 0.0f) {
-                total = __fadd_rn(total, (f2u(total) & 1u) ? d.y : d.x);
+                total = __fadd_rn(total, (f2u(total) & 1u) ? d.y : d.x);      // exact
               } else {
-                const float* yp = Y + t * DCB_XPITCH;
-                #pragma unroll
-                for (int e = 0; e < DCB_E; e++) total = __fadd_rn(total, yp[e]);
+                const float* yp = Y + __float_as_int(d.y) * DCB_XPITCH;
+                const float4 v0 = *reinterpret_cast<const float4*>(yp), v1 = *reinterpret_cast<const float4*>(yp + 4);
+                const float4 v2 = *reinterpret_cast<const float4*>(yp + 8), v3 = *reinterpret_cast<const float4*>(yp + 12);
+                total = __fadd_rn(total, v0.x); total = __fadd_rn(total, v0.y); total = __fadd_rn(total, v0.z); total = __fadd_rn(total, v0.w);
+                total = __fadd_rn(total, v1.x); total = __fadd_rn(total, v1.y); total = __fadd_rn(total, v1.z); total = __fadd_rn(total, v1.w);
+                total = __fadd_rn(total, v2.x); total = __fadd_rn(total, v2.y); total = __fadd_rn(total, v2.z); total = __fadd_rn(total, v2.w);
+                total = __fadd_rn(total, v3.x); total = __fadd_rn(total, v3.y); total = __fadd_rn(total, v3.z); total = __fadd_rn(total, v3.w);
               }
-              t = tn; d = dn;
+              d = dn;
             }
-            #undef DCB_NEXT_STOP
+#ifdef DCB_DEBUG_MED
+            { const long long t1 = clock64(); atomicAdd(&g_dbg_walk[0], (unsigned long long)(t1 - dbg_l2_t0)); atomicAdd(&g_dbg_walk[1], (unsigned long long)(t1 - dbg_w_t0)); atomicAdd(&g_dbg_walk[2], 1ull); atomicAdd(&g_dbg_walk[3], (unsigned long long)ns); }
+#endif
             const float med = __fdiv_rn(total, (float)cnt);
             const int ty = (Y[0] != Y[0]) ? 0 : type_from_max(mx);
             sm.med = med; sm.type = ty;
@@ -532,7 +564,9 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
       if (lane >= o) incl += t;
     }
     if (lane == 31) sm.warp_tot[par][warp] = incl;
+    if (tid == DCB_TKT_TID) sm.tkt[par] = tk;
     const bool fast_pack = __syncthreads_and(total >= 32u || total == 0u);      // barrier 2
+    const uint32_t nn = sm.tkt[par];
     uint32_t warp_base = 0, tile_bits = 0;
     #pragma unroll
     for (int w = 0; w < DCB_NT / 32; w++) {
@@ -617,7 +651,7 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_slo
     // ---- 7. next tile ------------------------------------------------------------------------------------------
     pend_tile = tile; pend_bits = tile_bits;
     par ^= 1;
-    cur = nxt;
+    cur = nxt; nxt = nn;
     if (cur >= a.num_tiles) break;
   }
 
