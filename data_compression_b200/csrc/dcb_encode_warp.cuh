@@ -220,8 +220,10 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_war
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   WarpBuf& sm = reinterpret_cast<WarpBuf*>(dcb_warp_smem)[warp];
   const uint32_t K = a.num_tiles;
-  const uint32_t nw = gridDim.x * (DCB_NT / 32);
-  uint32_t c = blockIdx.x * (DCB_NT / 32) + warp;
+  // chunks are handed out by a ticket counter, one chunk ahead (the next chunk's statistics are folded in during this one)
+  uint32_t c = 0u, cn = 0u;
+  if (lane == 0) { c = atomicAdd(a.ticket, 1u); cn = atomicAdd(a.ticket, 1u); }
+  c = __shfl_sync(0xffffffffu, c, 0); cn = __shfl_sync(0xffffffffu, cn, 0);
   if (c >= K) return;
 
   const bool submin = (a.flags & 1u) != 0;            // DCB_F_SUBTRACT_MIN
@@ -329,8 +331,9 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_war
     }
 
     // ---- the rounds ----------------------------------------------------------------------------------------------
-    const uint32_t cn = c + nw;
     const bool has_next = fold_next && cn < K;
+    uint32_t tk = 0u;
+    if (lane == 0) tk = atomicAdd(a.ticket, 1u);        // the chunk after next (lands while this chunk is encoded)
     const uint64_t nbase = (uint64_t)cn * DCB_TILE;
     const uint64_t nend = has_next ? min(nbase + DCB_TILE, a.n) : 0ull;
     const int nrn = has_next ? (int)((nend - nbase + DCB_WR - 1) / DCB_WR) : 0;
@@ -583,5 +586,6 @@ __global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_war
     }
     if (!has_next) break;
     c = cn;
+    cn = __shfl_sync(0xffffffffu, tk, 0);
   }
 }
