@@ -353,10 +353,10 @@ def run_ours(a):
         pass
     B = float(total_bytes)
     alg_c, alg_d = 4.0 * n + B, B + 4.0 * n
-    # one-tile chunks take the slot path: an encoder kernel (warp-autonomous for CT=5/6/11, block per chunk for CT=7) plus the
+    # one-tile chunks take the slot path: the warp-autonomous encoder kernel plus the
     # compaction kernel; the CUDA-event bracket of `compress` covers both (and the workspace memset), which is what is divided
     slot_path = (a.chunk == 4096) or n <= 4096
-    enc_kernel = ("dcb_encode_slots_kernel" if a.ct in (7, 9) else "dcb_encode_warp_kernel") if slot_path else "dcb_encode_kernel"
+    enc_kernel = "dcb_encode_warp_kernel" if slot_path else "dcb_encode_kernel"
     dom = enc_kernel if tc_ms >= td_ms else "dcb_decode_kernel"
     ach = (alg_c / (tc_ms * 1e-3) if tc_ms >= td_ms else alg_d / (td_ms * 1e-3)) / 1e9
     value = 4.0 * n * world * a.steps / (t_total * 1e-3) / 1e9

@@ -93,16 +93,15 @@ static uint64_t ws_slots_at(uint64_t n) {
   const uint64_t K = num_tiles(n);
   return (ws_head_bytes(n) + 4 * ws_groups(K) + 4 * K + 255) & ~(uint64_t)255;
 }
-// Encoder for one-tile chunks.  Default (3): the warp-autonomous kernel for CT=5/6/11, the block-per-chunk slot kernel for
-// CT=7 (its medium needs block-wide exact sums; measured faster there).  DCB_ENCODER = warp | slots | single forces one
-// kernel for every CT (A/B runs, and the parity tests cover all three).
+// Encoder for one-tile chunks.  Default: the warp-autonomous kernel (fastest for every CT: 0.42 / 0.61 ms against 0.47 / 0.73 ms
+// of the block-per-chunk slot kernel and 0.65 / 0.96 ms of the single-pass kernel, CT=5 / CT=7 on the smooth 2^28 field).
+// DCB_ENCODER = warp | slots | single forces one kernel (A/B runs; the parity tests cover all three).
 static int encoder_choice() {
   static const int v = [] {
     const char* e = getenv("DCB_ENCODER");
     if (getenv("DCB_SINGLE_PASS") || (e && !strcmp(e, "single"))) return 0;
     if (e && !strcmp(e, "slots")) return 1;
-    if (e && !strcmp(e, "warp")) return 2;
-    return 3;
+    return 2;
   }();
   return v;
 }
@@ -141,15 +140,15 @@ static cudaError_t launch_encode(const EncArgs& a, cudaStream_t st) {
 template <int CT>
 static cudaError_t launch_encode_warp(const EncArgs& a, const CompactArgs& ca, cudaStream_t st) {
   static bool attr_set = false;
-  const int smem = (int)(sizeof(WarpBuf) * (DCB_NT / 32));
+  const int smem = (int)(sizeof(WarpBuf) * (DCB_WNT / 32));
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(dcb_encode_warp_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  const uint64_t blocks = ((uint64_t)a.num_tiles + DCB_NT / 32 - 1) / (DCB_NT / 32);
-  const unsigned grid = (unsigned)min(blocks, (uint64_t)num_sms() * DCB_SLOT_BLOCKS_PER_SM);
-  dcb_encode_warp_kernel<CT><<<grid, DCB_NT, smem, st>>>(a);
+  const uint64_t blocks = ((uint64_t)a.num_tiles + DCB_WNT / 32 - 1) / (DCB_WNT / 32);
+  const unsigned grid = (unsigned)min(blocks, (uint64_t)num_sms() * (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 : DCB_WARP_BLOCKS));
+  dcb_encode_warp_kernel<CT><<<grid, DCB_WNT, smem, st>>>(a);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   dcb_compact_kernel<<<(unsigned)ws_groups(ca.K), DCB_COMPACT_NT, 0, st>>>(ca);
@@ -253,7 +252,7 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
     ca.slots = a.slots; ca.sizes = a.sizes; ca.gsum = a.gsum; ca.last_tile_bits = a.last_tile_bits; ca.K = K;
     ca.out = d_stream; ca.offsets = d_offsets; ca.last_bits = a.last_bits;
     cudaError_t es;
-    if (encoder_choice() == 2 || (encoder_choice() == 3 && bct != CT_MASK)) {
+    if (encoder_choice() == 2) {
       switch (bct) {
         case CT_BITWISE: es = launch_encode_warp<CT_BITWISE>(a, ca, st); break;
         case CT_NP: es = launch_encode_warp<CT_NP>(a, ca, st); break;

@@ -16,6 +16,15 @@
 #pragma once
 #include "dcb_encode_slots.cuh"
 
+#ifndef DCB_WARP_BLOCKS_CT7
+#define DCB_WARP_BLOCKS_CT7 2        // CT=7 carries more live state: 2 blocks per SM (up to 128 registers) instead of spilling at 80
+#endif
+#ifndef DCB_WNT
+#define DCB_WNT 256                 // threads per block of the warp kernel (its warps are independent)
+#endif
+#ifndef DCB_WARP_BLOCKS
+#define DCB_WARP_BLOCKS 2          // 16 warps per SM with up to 128 registers beat 24 warps at 80 (0.47 -> 0.43 ms, CT=5 smooth)
+#endif
 #define DCB_WR 512                  // elements per round (32 lanes x 16)
 #define DCB_WWORDS 520              // words of the round buffer: 512 codes of <= 32 bits + carry word + slack
 
@@ -161,6 +170,7 @@ __device__ __noinline__ void exact_medium(const EncArgs& a, WarpBuf& sm, uint64_
     }
     if (j == 0) y0 = __shfl_sync(0xffffffffu, y[0], 0);
     float d0 = -1.0f, d1 = -1.0f;                        // < 0: not a transducer
+    uint32_t ebits = 0u;
     if (!slow) {
       const float q0 = __fadd_rn(__fadd_rn(y[0], y[1]), __fadd_rn(y[2], y[3]));
       const float q1 = __fadd_rn(__fadd_rn(y[4], y[5]), __fadd_rn(y[6], y[7]));
@@ -184,27 +194,44 @@ __device__ __noinline__ void exact_medium(const EncArgs& a, WarpBuf& sm, uint64_
         #pragma unroll
         for (int e = 0; e < DCB_E; e++) { c0 = __fadd_rn(c0, y[e]); c1 = __fadd_rn(c1, y[e]); }
         d0 = __fsub_rn(c0, r0); d1 = __fsub_rn(c1, r1);  // exact: both ends lie on the grid of one binade
+        ebits = elo;
       }
     } else {
       #pragma unroll
       for (int e = 0; e < DCB_E; e++) if (e < vcnt) ymx = fmaxf(ymx, y[e]);
     }
-    // S travels from lane to lane
-    float Sout = S;
-    for (int k = 0; k < 32; k++) {
-      const float Sin = (k == 0) ? S : __shfl_sync(0xffffffffu, Sout, k - 1);
-      if (lane == k) {
-        if (d0 >= 0.0f) {
-          Sout = __fadd_rn(Sin, (f2u(Sin) & 1u) ? d1 : d0);
-        } else {
-          float t = Sin;
-          #pragma unroll
-          for (int e = 0; e < DCB_E; e++) t = __fadd_rn(t, y[e]);
-          Sout = t;
-        }
+    // Runs of consecutive transducer lanes in the same binade compose (associatively) into one transducer: segmented
+    // warp scan, (E then O)_p = E_p + O_{p ^ parity(E_p / q)}, every sum exact.  Then S walks over the run ends and the
+    // lanes that straddle a binade (their 16 values one by one): one or two stops in most rounds.
+    const bool certain = d0 >= 0.0f;
+    const unsigned cm = __ballot_sync(0xffffffffu, certain);
+    const uint32_t eprev = __shfl_up_sync(0xffffffffu, ebits, 1);
+    const bool head = certain && (lane == 0 || !((cm >> (lane - 1)) & 1u) || eprev != ebits);
+    const unsigned hm = __ballot_sync(0xffffffffu, head);
+    const int rs = 31 - __clz((int)(hm & (0xFFFFFFFFu >> (31 - lane))));
+    const float rb = u2f(ebits << 23);
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const float e0 = __shfl_up_sync(0xffffffffu, d0, o), e1 = __shfl_up_sync(0xffffffffu, d1, o);
+      if (certain && lane - o >= rs) {
+        const bool p0 = (f2u(__fadd_rn(rb, e0)) & 1u) != 0u, p1 = (f2u(__fadd_rn(rb, e1)) & 1u) != 0u;
+        const float n0 = __fadd_rn(e0, p0 ? d1 : d0), n1 = __fadd_rn(e1, p1 ? d0 : d1);
+        d0 = n0; d1 = n1;
       }
     }
-    S = __shfl_sync(0xffffffffu, Sout, 31);
+    const bool tail = certain && (lane == 31 || ((hm >> (lane + 1)) & 1u) || !((cm >> (lane + 1)) & 1u));
+    unsigned m = __ballot_sync(0xffffffffu, !certain || tail);
+    while (m) {                                          // warp-uniform: S is the same in every lane
+      const int k = __ffs((int)m) - 1;
+      m &= m - 1u;
+      if ((cm >> k) & 1u) {
+        const float k0 = __shfl_sync(0xffffffffu, d0, k), k1 = __shfl_sync(0xffffffffu, d1, k);
+        S = __fadd_rn(S, (f2u(S) & 1u) ? k1 : k0);       // exact
+      } else {
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) S = __fadd_rn(S, __shfl_sync(0xffffffffu, y[e], k));
+      }
+    }
   }
   if (slow) {
     #pragma unroll
@@ -215,7 +242,7 @@ __device__ __noinline__ void exact_medium(const EncArgs& a, WarpBuf& sm, uint64_
 }
 
 template <int CT>
-__global__ void __launch_bounds__(DCB_NT, DCB_SLOT_BLOCKS_PER_SM) dcb_encode_warp_kernel(const EncArgs a) {
+__global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 : DCB_WARP_BLOCKS)) dcb_encode_warp_kernel(const EncArgs a) {
   extern __shared__ __align__(16) unsigned char dcb_warp_smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   WarpBuf& sm = reinterpret_cast<WarpBuf*>(dcb_warp_smem)[warp];
