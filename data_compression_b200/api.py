@@ -30,7 +30,7 @@ EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb",
            "dcb_chunk_stats", "dcb_chunk_medium", "dcb_flip_bits", "dcb_compress_host", "dcb_decompress_host",
            "dcb_last_stream_bits", "dcb_gather_face", "dcb_scatter_face", "dcb_himeno_jacobi",
            "dcb_himeno_copy_interior", "dcb_max_stream_bytes_f64", "dcb_workspace_bytes_f64", "dcb_compress_f64",
-           "dcb_decompress_f64", "dcb_chunk_stats_f64"]
+           "dcb_decompress_f64", "dcb_chunk_stats_f64", "dcb_profile_enable", "dcb_profile_last_ms"]
 
 _lib = None
 
@@ -56,6 +56,10 @@ def lib():
         for f in ("dcb_num_chunks", "dcb_max_stream_bytes", "dcb_workspace_bytes"):
             getattr(L, f).restype = u64
             getattr(L, f).argtypes = [u64, u64]
+        L.dcb_profile_enable.restype = i32
+        L.dcb_profile_enable.argtypes = [i32]
+        L.dcb_profile_last_ms.restype = i32
+        L.dcb_profile_last_ms.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_float)]
         L.dcb_compress.restype = i32
         L.dcb_compress.argtypes = [i32, vp, u64, u64, dbl, u32, i32, u32, vp, u64, vp, vp, vp, vp, vp, vp, u64, vp]
         L.dcb_decompress.restype = i32

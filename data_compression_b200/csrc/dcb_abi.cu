@@ -137,6 +137,24 @@ static cudaError_t launch_encode(const EncArgs& a, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+// Optional per-kernel timing of the slot path (bench.py's roofline line): when enabled, dcb_compress records CUDA events on its
+// stream around the encoder kernel and around the compaction kernel; dcb_profile_last_ms reads them back.
+static thread_local bool g_prof_on = false;
+static thread_local cudaEvent_t g_prof_ev[3] = {nullptr, nullptr, nullptr};
+extern "C" int dcb_profile_enable(int on) {
+  if (on && !g_prof_ev[0]) for (int i = 0; i < 3; i++) CK(cudaEventCreate(&g_prof_ev[i]));
+  g_prof_on = on != 0;
+  return DCB_OK;
+}
+extern "C" int dcb_profile_last_ms(float* encode_ms, float* compact_ms) {
+  if (!g_prof_ev[0]) return DCB_EINVAL;
+  CK(cudaEventSynchronize(g_prof_ev[2]));
+  if (encode_ms) CK(cudaEventElapsedTime(encode_ms, g_prof_ev[0], g_prof_ev[1]));
+  if (compact_ms) CK(cudaEventElapsedTime(compact_ms, g_prof_ev[1], g_prof_ev[2]));
+  return DCB_OK;
+}
+#define PROF_MARK(i) do { if (g_prof_on) { cudaError_t pe_ = cudaEventRecord(g_prof_ev[i], st); if (pe_ != cudaSuccess) return pe_; } } while (0)
+
 template <int CT>
 static cudaError_t launch_encode_warp(const EncArgs& a, const CompactArgs& ca, cudaStream_t st) {
   static bool attr_set = false;
@@ -148,10 +166,13 @@ static cudaError_t launch_encode_warp(const EncArgs& a, const CompactArgs& ca, c
   }
   const uint64_t blocks = ((uint64_t)a.num_tiles + DCB_WNT / 32 - 1) / (DCB_WNT / 32);
   const unsigned grid = (unsigned)min(blocks, (uint64_t)num_sms() * (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 : DCB_WARP_BLOCKS));
+  PROF_MARK(0);
   dcb_encode_warp_kernel<CT><<<grid, DCB_WNT, smem, st>>>(a);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
+  PROF_MARK(1);
   dcb_compact_kernel<<<(unsigned)ws_groups(ca.K), DCB_COMPACT_NT, 0, st>>>(ca);
+  PROF_MARK(2);
   return cudaGetLastError();
 }
 
@@ -164,10 +185,13 @@ static cudaError_t launch_encode_slots(const EncArgs& a, const CompactArgs& ca, 
     attr_set = true;
   }
   const unsigned grid = (unsigned)min((uint64_t)a.num_tiles, (uint64_t)num_sms() * DCB_SLOT_BLOCKS_PER_SM);
+  PROF_MARK(0);
   dcb_encode_slots_kernel<CT><<<grid, DCB_NT, sizeof(SlotSmem), st>>>(a);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
+  PROF_MARK(1);
   dcb_compact_kernel<<<(unsigned)ws_groups(ca.K), DCB_COMPACT_NT, 0, st>>>(ca);
+  PROF_MARK(2);
   return cudaGetLastError();
 }
 

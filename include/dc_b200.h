@@ -79,6 +79,12 @@ int dcb_decompress(int ct, const uint8_t* d_stream, const uint64_t* d_chunk_offs
                    uint32_t fixed_mask17, const float* d_chunk_min, const float* d_chunk_medium,
                    const int32_t* d_chunk_type, float* d_out, int32_t* d_status, void* cuda_stream);
 
+/* Measurement aid (bench.py): with dcb_profile_enable(1) the calling thread's dcb_compress calls that take the slot path
+ * (one chunk == one tile) record CUDA events around the encoder kernel and the compaction kernel; dcb_profile_last_ms
+ * waits for the last such call and returns the two durations.  No effect on results. */
+int dcb_profile_enable(int on);
+int dcb_profile_last_ms(float* encode_kernel_ms, float* compact_kernel_ms);
+
 /* do_crc32 (dataCompression.c:5524) of each chunk's stream, as a stand-alone pass */
 int dcb_crc32_chunks(const uint8_t* d_stream, const uint64_t* d_chunk_offsets, uint64_t num_chunks,
                      uint32_t* d_chunk_crc, void* cuda_stream);
