@@ -25,7 +25,7 @@ for li, r in enumerate(rows[2:]):
             if k in hdr:
                 i = hdr.index(k)
                 f.write('%-70s %s %s\n' % (k, r[i], units[i]))
-        env = dict(os.environ, LAUNCH=str(li))
+        env = dict(os.environ, LAUNCH=str(li * int(os.environ.get('SRC_SECTIONS_PER_LAUNCH', '1'))))   # some reports list every launch twice on the source page
         seg = subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), 'ncuseg.py'), rep], capture_output=True, text=True, env=env).stdout
         keep = seg[seg.index('total inst'):] if 'total inst' in seg else seg
         f.write('\n# stall mix (% of warp samples) and SASS segments by execution count: first-last index, #instr, times executed,\n# share of executed instructions, share of samples, first instruction, top stalls\n')
