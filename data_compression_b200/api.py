@@ -30,7 +30,8 @@ EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb",
            "dcb_chunk_stats", "dcb_chunk_medium", "dcb_flip_bits", "dcb_compress_host", "dcb_decompress_host",
            "dcb_last_stream_bits", "dcb_gather_face", "dcb_scatter_face", "dcb_himeno_jacobi",
            "dcb_himeno_copy_interior", "dcb_max_stream_bytes_f64", "dcb_workspace_bytes_f64", "dcb_compress_f64",
-           "dcb_decompress_f64", "dcb_chunk_stats_f64", "dcb_profile_enable", "dcb_profile_last_ms"]
+           "dcb_decompress_f64", "dcb_chunk_stats_f64", "dcb_profile_enable", "dcb_profile_last_ms",
+           "dcb_hm_length", "dcb_hamming_encode", "dcb_hamming_decode"]
 
 _lib = None
 
@@ -56,6 +57,12 @@ def lib():
         for f in ("dcb_num_chunks", "dcb_max_stream_bytes", "dcb_workspace_bytes"):
             getattr(L, f).restype = u64
             getattr(L, f).argtypes = [u64, u64]
+        L.dcb_hm_length.restype = i32
+        L.dcb_hm_length.argtypes = [i32]
+        L.dcb_hamming_encode.restype = i32
+        L.dcb_hamming_encode.argtypes = [vp, u64, u32, vp, vp, vp]
+        L.dcb_hamming_decode.restype = i32
+        L.dcb_hamming_decode.argtypes = [vp, u64, u32, vp, vp, vp]
         L.dcb_profile_enable.restype = i32
         L.dcb_profile_enable.argtypes = [i32]
         L.dcb_profile_last_ms.restype = i32
@@ -331,6 +338,35 @@ def flip_bits(stream, bit_indices):
     idx = torch.as_tensor(bit_indices, dtype=torch.int64, device=stream.device)
     with torch.cuda.device(stream.device):
         check(lib().dcb_flip_bits(_ptr(stream), _ptr(idx), idx.numel(), _cur_stream(stream.device)), "dcb_flip_bits")
+
+
+def hm_length(k):
+    """hmLength (dataCompression.c:5587): check bits of a Hamming block of k data bits."""
+    return int(lib().dcb_hm_length(int(k)))
+
+
+def hamming_encode(stream, total_bytes, block_bytes):
+    """hamming_encode (dataCompression.c:5742) of every block of a finished device stream, as impl/pingpong.c:296-311 calls it.
+    Returns (check, r): int32 tensors [blocks]; check[b] bit i = c[i] (i < r[b]), bit r[b] = the SECDED parity bit."""
+    import torch
+    nb = max((int(total_bytes) + int(block_bytes) - 1) // int(block_bytes), 1)
+    chk = torch.zeros(nb, dtype=torch.int32, device=stream.device)
+    r = torch.zeros(nb, dtype=torch.int32, device=stream.device)
+    with torch.cuda.device(stream.device):
+        check(lib().dcb_hamming_encode(_ptr(stream), int(total_bytes), int(block_bytes), _ptr(chk), _ptr(r),
+                                       _cur_stream(stream.device)), "dcb_hamming_encode")
+    return chk, r
+
+
+def hamming_decode(stream, total_bytes, block_bytes, chk):
+    """hamming_decode (dataCompression.c:5752) of every block: single-bit errors are rectified in `stream` / `chk` in place.
+    Returns the error type of every block (0 none, 1 two-bit, 2 parity bit, 3 one bit)."""
+    import torch
+    et = torch.zeros(chk.numel(), dtype=torch.int32, device=stream.device)
+    with torch.cuda.device(stream.device):
+        check(lib().dcb_hamming_decode(_ptr(stream), int(total_bytes), int(block_bytes), _ptr(chk), _ptr(et),
+                                       _cur_stream(stream.device)), "dcb_hamming_decode")
+    return et
 
 
 def gather_face(p, ijk, v, imax, jmax, kmax, out=None):

@@ -18,6 +18,7 @@
 #include "dcb_crc.cuh"
 #include "dcb_face.cuh"
 #include "dcb_f64.cuh"
+#include "dcb_hamming.cuh"
 static int ensure_crc_tables(cudaStream_t st);
 #include <math.h>
 #include <stdio.h>
@@ -750,6 +751,31 @@ extern "C" int dcb_debug_timeline(long long* host_dst) {
   return DCB_OK;
 }
 #endif
+
+// ---- Hamming SECDED over blocks of the finished stream (CT=10) ------------------------------------------------------------
+extern "C" int dcb_hm_length(int k) { return k < 0 ? -1 : hm_length(k); }
+static int hamming_launch(uint8_t* d_bits, uint64_t total, uint32_t block_bytes, uint32_t* d_check, int32_t* d_r,
+                          int32_t* d_et, int decode, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (total == 0) return DCB_OK;
+  if (!d_bits || !d_check || block_bytes == 0 || block_bytes > (1u << 26)) return DCB_EINVAL;   // r <= 30 fits the packed word
+  const uint64_t blocks = (total + block_bytes - 1) / block_bytes;
+  if (blocks > 0x7FFFFFFFull) return DCB_EINVAL;
+  HmArgs a;
+  a.bits = d_bits; a.total_bytes = total; a.block_bytes = block_bytes; a.check = d_check; a.r_out = d_r; a.error_type = d_et;
+  a.decode = decode;
+  dcb_hamming_kernel<<<(unsigned)blocks, DCB_HM_NT, 0, (cudaStream_t)stream>>>(a);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+extern "C" int dcb_hamming_encode(const uint8_t* d_bits, uint64_t total_bytes, uint32_t block_bytes, uint32_t* d_check,
+                                  int32_t* d_r, void* stream) {
+  return hamming_launch(const_cast<uint8_t*>(d_bits), total_bytes, block_bytes, d_check, d_r, nullptr, 0, stream);
+}
+extern "C" int dcb_hamming_decode(uint8_t* d_bits, uint64_t total_bytes, uint32_t block_bytes, uint32_t* d_check,
+                                  int32_t* d_error_type, void* stream) {
+  return hamming_launch(d_bits, total_bytes, block_bytes, d_check, nullptr, d_error_type, 1, stream);
+}
 
 #ifdef DCB_DEBUG_MED
 extern "C" int dcb_debug_walk(unsigned long long* host_dst) {

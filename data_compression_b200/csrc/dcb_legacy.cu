@@ -343,3 +343,103 @@ extern "C" double strtodbl(char* str) {
   memcpy(&d, &c, 8);
   return d;
 }
+
+
+// ---- CT=10: Hamming SECDED blocks of the finished stream (dataCompression.h:144-158) -------------------------------------
+static double g_ber = -1.0;                        // < 0: not set yet -> environment, then the header default (dataCompression.h:4)
+extern "C" void dc_set_ber(double ber) { g_ber = ber; }
+extern "C" double dc_get_ber(void) {
+  if (g_ber < 0.0) {
+    const char* e = getenv("DC_BER");
+    g_ber = (e && atof(e) > 0.0) ? atof(e) : 1e-6;
+  }
+  return g_ber;
+}
+extern "C" int hmLength(int k) { return dcb_hm_length(k); }                                   // dataCompression.c:5587
+extern "C" int block_size(int data_bytes) {                                                    // :5868-5878
+  const double ber = dc_get_ber();
+  const uint64_t bits = (uint64_t)(1 / ber);
+  const uint64_t bytes = bits / 8;
+  int bs = data_bytes;
+  if ((uint64_t)bs > bytes) bs = (int)bytes;
+  return bs;
+}
+extern "C" uint64_t get_random_int(uint64_t from, uint64_t to) { return (uint64_t)rand() % (to - from + 1) + from; }   // :5536
+extern "C" void bit_flip(unsigned char* bits, int bytes) {                                     // :5860-5866 (fault injection, host memory)
+  const int num = rand() % (bytes * 8);
+  bits[num / 8] ^= (unsigned char)(1 << (7 - num % 8));
+}
+extern "C" void cast_bits_to_char(unsigned char* bits, char* data, int bytes) {                // :5712-5722
+  for (int i = 0; i < bytes; i++)
+    for (int j = 0; j < 8; j++) data[i * 8 + j] = (char)(((bits[i] >> (7 - j)) & 1) + '0');
+}
+
+// one block on the device: stage the bytes, run dcb_hamming_{encode,decode}, read the packed check word back
+static uint32_t hm_pos_host(uint32_t d) {             // codeword position of data bit d (powers of two hold check bits)
+  uint32_t m = d + 1, t = 0;
+  while ((1u << t) <= m) t++;
+  uint32_t j = m + t;
+  if (j >> t) j++;
+  return j;
+}
+static uint32_t hamming_device(unsigned char* bits, int bytes, uint32_t check_in, int decode, int* error_type, uint32_t* err_pos) {
+  uint8_t* d_b = nullptr; uint32_t* d_c = nullptr; int32_t* d_e = nullptr;
+  uint32_t check = check_in; int32_t et = 0;
+  if (cudaMalloc(&d_b, (size_t)bytes) != cudaSuccess || cudaMalloc(&d_c, 8) != cudaSuccess || cudaMalloc(&d_e, 8) != cudaSuccess)
+    die("hamming: cudaMalloc", DCB_ECUDA);
+  cudaMemcpy(d_b, bits, (size_t)bytes, cudaMemcpyHostToDevice);
+  cudaMemcpy(d_c, &check, 4, cudaMemcpyHostToDevice);
+  const int rc = decode ? dcb_hamming_decode(d_b, (uint64_t)bytes, (uint32_t)bytes, d_c, d_e, nullptr)
+                        : dcb_hamming_encode(d_b, (uint64_t)bytes, (uint32_t)bytes, d_c, nullptr, nullptr);
+  if (rc) die(decode ? "hamming_decode" : "hamming_encode", rc);
+  if (cudaMemcpy(&check, d_c, 4, cudaMemcpyDeviceToHost) != cudaSuccess) die("hamming: copy back", DCB_ECUDA);
+  if (decode) {
+    cudaMemcpy(&et, d_e, 4, cudaMemcpyDeviceToHost);
+    if (et == 3) {                                  // a rectified data bit: find it (for the reference's message), take it over
+      unsigned char* fixed = (unsigned char*)malloc((size_t)bytes);
+      if (!fixed) { printf("ERROR: Out of memory\n"); exit(1); }
+      cudaMemcpy(fixed, d_b, (size_t)bytes, cudaMemcpyDeviceToHost);
+      for (int i = 0; i < bytes; i++)
+        if (fixed[i] != bits[i]) {
+          const unsigned x = (unsigned)(fixed[i] ^ bits[i]);
+          int b = 0; while (!((x >> (7 - b)) & 1u)) b++;
+          *err_pos = hm_pos_host((uint32_t)(8 * i + b));
+          break;
+        }
+      memcpy(bits, fixed, (size_t)bytes);
+      free(fixed);
+    }
+    *error_type = et;
+  }
+  cudaFree(d_b); cudaFree(d_c); cudaFree(d_e);
+  return check;
+}
+extern "C" void hamming_encode(unsigned char* bits, char** c, int bytes, int* r) {             // :5742-5750
+  if (dcb_device_count() == 0) die("hamming_encode", DCB_ENODEVICE);
+  *r = dcb_hm_length(bytes * 8);
+  *c = (char*)malloc(sizeof(char) * (size_t)(*r + 1));
+  if (bytes <= 0) return;
+  const uint32_t check = hamming_device(bits, bytes, 0u, 0, nullptr, nullptr);
+  for (int i = 0; i <= *r; i++) (*c)[i] = (char)('0' + ((check >> i) & 1u));
+}
+extern "C" int hamming_decode(unsigned char* bits, char* c, int bytes, int r) {               // :5752-5779
+  if (dcb_device_count() == 0) die("hamming_decode", DCB_ENODEVICE);
+  if (bytes <= 0) return 0;
+  uint32_t check = 0u;
+  for (int i = 0; i <= r; i++) check |= (uint32_t)(c[i] == '1') << i;
+  int et = 0;
+  uint32_t pos = 0u;
+  const uint32_t fixed = hamming_device(bits, bytes, check, 1, &et, &pos);
+  switch (et) {                                                                               // the reference's own messages
+    case 0: break;
+    case 1: printf("two-bit error\n"); break;
+    case 2: printf("parity error\n"); break;
+    case 3:
+      if ((fixed ^ check) & ((1u << r) - 1u)) pos = (fixed ^ check) & ((1u << r) - 1u);   // a rectified check bit c[i] sits at position 2^i
+      printf("one bit error: pos = %d\n", (int)pos);
+      break;
+    default: printf("ERROR");
+  }
+  for (int i = 0; i <= r; i++) c[i] = (char)('0' + ((fixed >> i) & 1u));
+  return et;
+}

@@ -72,6 +72,19 @@ double  med_dataset_double(double* data, int num, int* type);                   
 void    doubletostr(double* a, char* str);                                                                    /* dataCompression.h:126 */
 double  strtodbl(char* str);                                                                                  /* dataCompression.h:128 */
 
+
+/* ---- CT=10: Hamming SECDED over blocks of the finished stream (impl/pingpong.c:212-222, :296-311, :487-505) ----
+ * BER is a compile-time macro in the reference (dataCompression.h:4); here dc_set_ber() / DC_BER, default 1e-6. */
+void     dc_set_ber(double ber);
+double   dc_get_ber(void);
+uint64_t get_random_int(uint64_t from, uint64_t to);                                                          /* dataCompression.h:144 */
+int      hmLength(int k);                                                                                     /* dataCompression.h:146 */
+void     cast_bits_to_char(unsigned char* bits, char* data, int bytes);                                       /* dataCompression.h:152 */
+void     hamming_encode(unsigned char* bits, char** c, int bytes, int* r);                                    /* dataCompression.h:153 */
+int      hamming_decode(unsigned char* bits, char* c, int bytes, int r);                                      /* dataCompression.h:154 */
+void     bit_flip(unsigned char* bits, int bytes);                                                            /* dataCompression.h:157 */
+int      block_size(int data_bytes);                                                                          /* dataCompression.h:158 */
+
 #ifdef __cplusplus
 }
 #endif

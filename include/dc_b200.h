@@ -100,6 +100,17 @@ int dcb_chunk_medium(const float* d_in, uint64_t n, float* d_medium, int32_t* d_
 /* bit_flip (dataCompression.c:5858) test hook: flips bit (7 - bit_index%8) of byte bit_index/8 for each index */
 int dcb_flip_bits(uint8_t* d_stream, const uint64_t* d_bit_indices, uint64_t count, void* cuda_stream);
 
+/* ---- Hamming SECDED of CT=10: hamming_encode / hamming_decode (dataCompression.c:5742, :5752), one
+ * call per block of the finished stream as impl/pingpong.c:296-311 / :487-505 make them.  Block b covers bytes
+ * [b*block_bytes, min(total_bytes, (b+1)*block_bytes)); its r = dcb_hm_length(8 * its bytes) check bits c[0..r-1] and the
+ * parity bit c[r] are packed into d_check[b] (bit i = c[i]).  Decode recomputes the syndrome, classifies (0 no error,
+ * 1 two-bit error, 2 parity bit, 3 one bit) and rectifies single errors in d_bits / d_check in place. */
+int dcb_hm_length(int k);                                                    /* hmLength, dataCompression.c:5587 */
+int dcb_hamming_encode(const uint8_t* d_bits, uint64_t total_bytes, uint32_t block_bytes, uint32_t* d_check,
+                       int32_t* d_r, void* cuda_stream);
+int dcb_hamming_decode(uint8_t* d_bits, uint64_t total_bytes, uint32_t block_bytes, uint32_t* d_check,
+                       int32_t* d_error_type, void* cuda_stream);
+
 /* ---- float64 codecs: the reference's *_double entry points ------------------------------------
  * dcb_compress_f64 replaces, per chunk, toSmallDataset_double (dataCompression.c:3522) -> [med_dataset_double (:3564) +
  * the mask chars, impl/k-means.c:525-530] -> myCompress_bitwise_double (:3189) / _np (:2633) / _mask (:1590) / _op (:355)

@@ -71,6 +71,11 @@ int dco_decompress_chunked_f64(int ct, const uint8_t* s, const uint64_t* offsets
                                double eb, int add_min, const double* chunk_min, int fixed_type,
                                uint32_t fixed_mask20, const uint32_t* chunk_mask20, const int32_t* chunk_type,
                                double* out);
+/* ---- Hamming SECDED of CT=10 (dc_oracle_hamming.c): hmLength :5587, hamming_encode :5742, hamming_decode :5752 ---- */
+int dco_hm_length(int k);
+int dco_hamming_encode(const uint8_t* bits, int bytes, char* c);          /* c: r + 1 chars; returns r */
+int dco_hamming_decode(uint8_t* bits, char* c, int bytes, int r);         /* returns the reference's error_type 0..3 */
+
 #ifdef __cplusplus
 }
 #endif

@@ -29,7 +29,7 @@ def eb_str(eb):
 
 
 def build_oracle():
-    srcs = [os.path.join(ORACLE_DIR, f) for f in ("dc_oracle.c", "dc_oracle_f64.c", "dc_oracle.h")]
+    srcs = [os.path.join(ORACLE_DIR, f) for f in ("dc_oracle.c", "dc_oracle_f64.c", "dc_oracle_hamming.c", "dc_oracle.h")]
     if (not os.path.exists(ORACLE_SO)) or os.path.getmtime(ORACLE_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", ORACLE_DIR, "_build/libdc_oracle.so"], stdout=subprocess.DEVNULL)
     return ORACLE_SO
@@ -477,3 +477,57 @@ def ref_mask_decode_defined_f64(type_, mask20, eb):
         return False
     k0 = max(m - 8, 0)
     return (type_ + 2 + k0 != 12) and (type_ + 2 + m != 12)
+
+
+# ---- Hamming SECDED of CT=10 (oracle/dc_oracle_hamming.c; reference impl/dataCompression.c:5544-5878) ----
+def _hm_oracle():
+    lib = oracle()
+    lib.dco_hm_length.restype = C.c_int
+    lib.dco_hm_length.argtypes = [C.c_int]
+    lib.dco_hamming_encode.restype = C.c_int
+    lib.dco_hamming_encode.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
+    lib.dco_hamming_decode.restype = C.c_int
+    lib.dco_hamming_decode.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int]
+    return lib
+
+
+def o_hm_length(k):
+    return int(_hm_oracle().dco_hm_length(int(k)))
+
+
+def o_hamming_encode(bits):
+    """-> (r, check string of r + 1 chars '0'/'1')"""
+    bits = np.ascontiguousarray(bits, dtype=np.uint8)
+    buf = C.create_string_buffer(64)
+    r = _hm_oracle().dco_hamming_encode(bits.ctypes.data, int(bits.size), buf)
+    return int(r), buf.raw[:r + 1]
+
+
+def o_hamming_decode(bits, c, r):
+    """bits (uint8 array) and c (bytes) may hold errors -> (error_type, corrected bits, corrected c)"""
+    bits = np.array(bits, dtype=np.uint8, copy=True)
+    cb = C.create_string_buffer(bytes(c), len(c) + 1)
+    t = _hm_oracle().dco_hamming_decode(bits.ctypes.data, cb, int(bits.size), int(r))
+    return int(t), bits, cb.raw[:r + 1]
+
+
+def ref_hamming_encode(bits, eb=0.01):
+    """The compiled reference's hamming_encode (impl/dataCompression.c:5742)."""
+    lib = RefLib(eb).lib
+    bits = np.ascontiguousarray(bits, dtype=np.uint8)
+    cp, r = C.c_char_p(), C.c_int()
+    lib.hamming_encode.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.c_int, C.POINTER(C.c_int)]
+    lib.hamming_encode.restype = None
+    lib.hamming_encode(bits.ctypes.data, C.byref(cp), int(bits.size), C.byref(r))
+    return r.value, C.string_at(cp, r.value + 1)
+
+
+def ref_hamming_decode(bits, c, r, eb=0.01):
+    """The compiled reference's hamming_decode (:5752); its messages go to the process's stdout."""
+    lib = RefLib(eb).lib
+    bits = np.array(bits, dtype=np.uint8, copy=True)
+    cb = C.create_string_buffer(bytes(c), len(c) + 1)
+    lib.hamming_decode.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int]
+    lib.hamming_decode.restype = C.c_int
+    t = lib.hamming_decode(bits.ctypes.data, cb, int(bits.size), int(r))
+    return int(t), bits, cb.raw[:r + 1]
