@@ -9,6 +9,12 @@ MPI messages of the reference's drivers.
   with the chunk table (size known from n and chunk_elems), then the stream bytes the header announced.
 * pingpong_hop_crc(): the CT=8/9 protocol of impl/pingpong.c:260-289 (sender) and :363-447 (receiver): stream,
   CRC, one-byte ack 'y'/'n', resend on 'n'.
+* bcast_compressed(): the collective wrappers of the float64 callers -- MPI_Bcast_bitwise_double
+  (impl/dataCompression.c:165-224: one padded message [int bytes][double min][payload]) and MPI_Bcast_bitwise{,_mask}_crc
+  (:968-1089, :1092-1197: bytes, min, payload, medium, type, crc broadcast; 'y'/'n' gathered at the root; the root re-sends
+  to every 'n' rank).  Here: the fixed-size table broadcast, the stream broadcast at its announced length (no padding to the
+  worst case), acks by all_gather (NCCL has no gather), point-to-point resends.  Frames carry float32 (api.Compressed) or
+  float64 (api.CompressedF64: double min, 20-bit masks) chunk tables.
 
 torch.distributed is the plumbing (backend "nccl" over NVLink on the GPU box, "gloo" in the CPU tests); the payload is
 whatever device the tensors live on.  Nothing here encodes or decodes.
@@ -37,9 +43,17 @@ def num_chunks(n, chunk_elems):
     return 1 if (chunk_elems <= 0 or chunk_elems >= n) else (n + chunk_elems - 1) // chunk_elems
 
 
-def table_words(K):
-    """int64 words of the header message: fixed header + offsets[K+1] + (min, medium, type, crc)[K] packed 2 x 32 bit."""
-    return HEADER_WORDS + (K + 1) + 2 * K
+F64_FLAG = 1 << 16        # header word 5: the frame carries a float64 chunk table
+
+
+def table_words(K, f64=False):
+    """int64 words of the header message: fixed header + offsets[K+1] + the chunk table --
+    float32: (min, medium, type, crc)[K] as 4K x 32 bit; float64: min[K] as 64 bit, then (mask20, type, crc, 0)[K] x 32 bit."""
+    return HEADER_WORDS + (K + 1) + (3 * K if f64 else 2 * K)
+
+
+def _is_f64(comp):
+    return hasattr(comp, "chunk_mask20")
 
 
 @dataclass
@@ -54,19 +68,30 @@ def pack_frame(comp):
     import torch
     K = comp.chunk_offsets.numel() - 1
     dev = comp.stream.device
-    t = torch.zeros(table_words(K), dtype=torch.int64, device=dev)
+    f64 = _is_f64(comp)
+    t = torch.zeros(table_words(K, f64), dtype=torch.int64, device=dev)
     eb_bits = int(np.array([comp.abs_error_bound], dtype=np.float64).view(np.int64)[0])
     total = int(comp.chunk_offsets[-1].item()) if K else 0
-    hdr = [MAGIC, comp.ct, comp.n, comp.chunk_elems, eb_bits, (comp.flags & 0xFF) | (comp.fixed_type << 8),
-           comp.fixed_mask17, total]
+    hdr = [MAGIC, comp.ct, comp.n, comp.chunk_elems, eb_bits,
+           (comp.flags & 0xFF) | ((comp.fixed_type & 0xFF) << 8) | (F64_FLAG if f64 else 0),
+           comp.fixed_mask20 if f64 else comp.fixed_mask17, total]
     t[:HEADER_WORDS] = torch.tensor(hdr, dtype=torch.int64, device=dev)
     t[HEADER_WORDS:HEADER_WORDS + K + 1] = comp.chunk_offsets
-    if K:
+    if K and not f64:
         side = torch.zeros(4 * K, dtype=torch.int32, device=dev)
         for i, f in enumerate((comp.chunk_min, comp.chunk_medium, comp.chunk_type, comp.chunk_crc)):
             if f is not None:
                 side[i * K:(i + 1) * K] = f[:K].view(torch.int32)
         t[HEADER_WORDS + K + 1:] = side.view(torch.int64)
+    elif K:
+        base = HEADER_WORDS + K + 1
+        if comp.chunk_min is not None:
+            t[base:base + K] = comp.chunk_min[:K].view(torch.int64)
+        side = torch.zeros(4 * K, dtype=torch.int32, device=dev)
+        for i, f in enumerate((comp.chunk_mask20, comp.chunk_type, comp.chunk_crc)):
+            if f is not None:
+                side[i * K:(i + 1) * K] = f[:K].view(torch.int32)
+        t[base + K:] = side.view(torch.int64)
     return Frame(t, comp.stream[:total])
 
 
@@ -80,9 +105,17 @@ def unpack_frame(frame, compressed_cls):
         raise ValueError("not a dcb200 frame")
     ct, n, chunk = hdr[1], hdr[2], hdr[3]
     eb = float(np.array([hdr[4]], dtype=np.int64).view(np.float64)[0])
-    flags, ftype, fmask = hdr[5] & 0xFF, hdr[5] >> 8, hdr[6]
+    flags, ftype, fmask = hdr[5] & 0xFF, (hdr[5] >> 8) & 0xFF, hdr[6]
     K = num_chunks(n, chunk)
     offs = t[HEADER_WORDS:HEADER_WORDS + K + 1].clone()
+    if hdr[5] & F64_FLAG:
+        # api.CompressedF64(ct, n, chunk_elems, eb, flags, fixed_type, fixed_mask20, stream, offsets, chunk_min, chunk_mask20,
+        #                   chunk_type, chunk_medium, chunk_crc)
+        base = HEADER_WORDS + K + 1
+        cmin = t[base:base + K].clone().view(torch.float64) if K else None
+        side = t[base + K:].contiguous().view(torch.int32) if K else torch.zeros(0, dtype=torch.int32)
+        return compressed_cls(ct, n, chunk, eb, flags, ftype, fmask, frame.stream, offs, cmin,
+                              side[0:K] if K else None, side[K:2 * K] if K else None, None, side[2 * K:3 * K] if K else None)
     side = t[HEADER_WORDS + K + 1:].contiguous().view(torch.int32) if K else torch.zeros(0, dtype=torch.int32)
     cmin = side[0:K].view(torch.float32) if K else None
     cmed = side[K:2 * K].view(torch.float32) if K else None
@@ -145,3 +178,54 @@ def pingpong_hop_crc(comp, peer, is_sender, n, chunk_elems, device, compressed_c
             if ok or resend >= max_resend:
                 return got, resend
             resend += 1
+
+
+def bcast_compressed(comp, root, n, chunk_elems, device, compressed_cls, f64=False, crc_fn: Optional[Callable] = None,
+                     corrupt_fn: Optional[Callable] = None, group=None):
+    """MPI_Bcast_bitwise_double / MPI_Bcast_bitwise{,_mask}_crc (impl/dataCompression.c:165-224, :968-1089, :1092-1197) on
+    torch.distributed.  `comp` is the root's compressed array (ignored elsewhere).  Every rank returns (the frame it
+    holds, resends): with crc_fn every non-root recomputes the per-chunk CRCs of what arrived [corrupt_fn: the reference's
+    BER fault model, called as corrupt_fn(frame, attempt) before the check], the 'y'/'n' acks are gathered, and the root
+    re-sends the stream point to point to every 'n' rank (once, as the reference does; the re-sent copy is not checked again)."""
+    import torch
+    import torch.distributed as dist
+    rank = dist.get_rank(group)
+    world = dist.get_world_size(group)
+    K = num_chunks(n, chunk_elems)
+    elem = 8 if f64 else 4
+    if rank == root:
+        f = pack_frame(comp)
+        t, stream = f.table, f.stream.contiguous()
+    else:
+        t = torch.empty(table_words(K, f64), dtype=torch.int64, device=device)
+    dist.broadcast(t, root, group=group)                       # data_bytes, min, medium, type, crc: one fixed-size message
+    total = int(t[HEADER_WORDS - 1].item())
+    cap = elem * n + 16
+    if total > cap:
+        raise ValueError("frame announces %d bytes for %d values" % (total, n))
+    if rank != root:
+        stream = torch.zeros(((total + 15) // 16) * 16 + 16, dtype=torch.uint8, device=device)
+    if total:
+        dist.broadcast(stream[:total], root, group=group)      # the payload at its real length (:1007)
+    got = comp if rank == root else unpack_frame(Frame(t, stream), compressed_cls)
+    resends = 0
+    if crc_fn is not None:
+        ok = True
+        if rank != root:
+            if corrupt_fn is not None:
+                corrupt_fn(got, 0)
+            ok = bool((crc_fn(got.stream, got.chunk_offsets)[:K] == got.chunk_crc[:K]).all().item())
+        ack = torch.tensor([ord("y") if ok else ord("n")], dtype=torch.uint8, device=device)
+        acks = [torch.zeros(1, dtype=torch.uint8, device=device) for _ in range(world)]
+        dist.all_gather(acks, ack, group=group)                # MPI_Gather of crc_ok (:1049)
+        bad = [r for r in range(world) if r != root and int(acks[r].item()) == ord("n")]
+        if rank == root:
+            for r in bad:                                      # :1053-1060
+                if total:
+                    dist.send(stream[:total], r, group=group)
+                resends += 1
+        elif rank in bad:
+            if total:
+                dist.recv(got.stream[:total], root, group=group)   # :1062-1065
+            resends = 1
+    return got, resends

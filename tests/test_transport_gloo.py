@@ -240,3 +240,102 @@ def test_halo_exchange_over_gloo_world2():
     for p in procs:
         p.join(timeout=60)
     assert all(r[1] == "ok" for r in res), res
+
+
+# ---- broadcast protocol of the float64 callers: MPI_Bcast_bitwise_double / _crc / _mask_crc ----------------
+@dataclass
+class HostCompressedF64:                   # same field order as api.CompressedF64
+    ct: int
+    n: int
+    chunk_elems: int
+    abs_error_bound: float
+    flags: int
+    fixed_type: int
+    fixed_mask20: int
+    stream: object
+    chunk_offsets: object
+    chunk_min: object
+    chunk_mask20: object
+    chunk_type: object
+    chunk_medium: object
+    chunk_crc: object
+
+
+def oracle_compressed_f64(x, ct, chunk, eb):
+    base = 5 if ct in (5, 8) else (7 if ct in (7, 9) else ct)
+    enc = ol.o_compress_chunked_f64(base, x, chunk, eb, want_crc=True)
+    pad = np.zeros(((enc["stream"].size + 31) // 16) * 16, np.uint8)
+    pad[:enc["stream"].size] = enc["stream"]
+    return HostCompressedF64(ct, x.size, chunk, eb, 1, 0, 0, torch.from_numpy(pad),
+                             torch.from_numpy(enc["offsets"].astype(np.int64)), torch.from_numpy(enc["chunk_min"]),
+                             torch.from_numpy(enc["chunk_mask20"].view(np.int32).copy()), torch.from_numpy(enc["chunk_type"]),
+                             None, torch.from_numpy(enc["chunk_crc"].view(np.int32).copy())), enc
+
+
+def _bcast_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        dev = torch.device("cpu")
+        root = 0
+        # (a) float64, CT=5, no CRC: MPI_Bcast_bitwise_double (impl/dataCompression.c:165-224); single chunk = the legacy shape
+        n, eb = 3000, 1e-4
+        xd = np.cumsum(np.random.default_rng(1).normal(0, 0.01, n)) + 3.0
+        comp, enc = oracle_compressed_f64(xd, 5, n, eb)
+        got, resends = tr.bcast_compressed(comp if rank == root else None, root, n, 0, dev, HostCompressedF64, f64=True)
+        assert resends == 0
+        total = int(got.chunk_offsets[-1])
+        assert np.array_equal(got.stream[:total].numpy(), enc["stream"]) and total == enc["stream"].size
+        assert torch.equal(got.chunk_min.view(torch.int64), torch.from_numpy(enc["chunk_min"]).view(torch.int64))
+        dec = ol.o_decompress_chunked_f64(5, dict(stream=got.stream[:total].numpy(), offsets=got.chunk_offsets.numpy().astype(np.uint64),
+                                                  chunk_min=got.chunk_min.numpy(), chunk_mask20=got.chunk_mask20.numpy().view(np.uint32),
+                                                  chunk_type=got.chunk_type.numpy()), n, n, eb)
+        assert np.array_equal(dec.view(np.uint64), ol.o_decompress_chunked_f64(5, enc, n, n, eb).view(np.uint64))
+        assert np.max(np.abs(dec - xd)) < 0.5                                 # buffer[i] = decompressed + min (:218-221)
+        # (b) float64, CT=9 (mask + CRC), chunked: MPI_Bcast_bitwise_mask_crc (:968-1089); rank 1's first copy is corrupted
+        n, chunk = 4096 * 3 + 50, 4096
+        xd = np.abs(np.sin(np.arange(n) * 1e-3)) * 7.0 + 1.0
+        comp, enc = oracle_compressed_f64(xd, 9, chunk, eb)
+
+        def crc_chunks64(stream, offsets):
+            return crc_chunks(stream, offsets)
+
+        def corrupt(got, attempt):
+            got.stream[int(got.chunk_offsets[1]) + 3] ^= 0x04               # the BER fault model (:1018-1027), second chunk
+
+        got, resends = tr.bcast_compressed(comp if rank == root else None, root, n, chunk, dev, HostCompressedF64, f64=True,
+                                           crc_fn=crc_chunks64, corrupt_fn=corrupt if rank == 1 else None)
+        assert resends == 1                                                  # root: one rank re-sent; rank 1: received it
+        total = int(got.chunk_offsets[-1])
+        assert np.array_equal(got.stream[:total].numpy(), enc["stream"])
+        assert np.array_equal(got.chunk_mask20.numpy().view(np.uint32), enc["chunk_mask20"])
+        assert np.array_equal(got.chunk_type.numpy(), enc["chunk_type"]) and np.array_equal(got.chunk_crc.numpy().view(np.uint32), enc["chunk_crc"])
+        # (c) float32 CT=8 frame through the same collective, clean delivery
+        x = make_field("noisy", 4096 * 2 + 9)
+        comp, enc = oracle_compressed(x, 8, 4096, 0.01)
+        got, resends = tr.bcast_compressed(comp if rank == root else None, root, x.size, 4096, dev, HostCompressed, crc_fn=crc_chunks)
+        assert resends == 0
+        assert np.array_equal(got.stream[:int(got.chunk_offsets[-1])].numpy(), enc["stream"])
+        q.put((rank, "ok"))
+    except Exception as e:  # pragma: no cover
+        import traceback
+        q.put((rank, "FAIL: %s\n%s" % (e, traceback.format_exc())))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_bcast_protocol_over_gloo_world2():
+    import torch.multiprocessing as mp
+    ol.build_oracle()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_bcast_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(r[1] == "ok" for r in res), res
