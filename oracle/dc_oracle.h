@@ -76,6 +76,10 @@ int dco_hm_length(int k);
 int dco_hamming_encode(const uint8_t* bits, int bytes, char* c);          /* c: r + 1 chars; returns r */
 int dco_hamming_decode(uint8_t* bits, char* c, int bytes, int r);         /* returns the reference's error_type 0..3 */
 
+/* ---- byte-wise codec CT=1 (dc_oracle_bytewise.c): myCompress :3977, myDecompress :3942 ---- */
+size_t dco_bytewise_compress(const float* x, size_t n, double eb, float* af, char* ac, int* ad);   /* returns the raw-float count */
+void dco_bytewise_decompress(const float* af, const char* ac, const int* ad, size_t nc, size_t n, float* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -29,7 +29,7 @@ def eb_str(eb):
 
 
 def build_oracle():
-    srcs = [os.path.join(ORACLE_DIR, f) for f in ("dc_oracle.c", "dc_oracle_f64.c", "dc_oracle_hamming.c", "dc_oracle.h")]
+    srcs = [os.path.join(ORACLE_DIR, f) for f in ("dc_oracle.c", "dc_oracle_f64.c", "dc_oracle_hamming.c", "dc_oracle_bytewise.c", "dc_oracle.h")]
     if (not os.path.exists(ORACLE_SO)) or os.path.getmtime(ORACLE_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", ORACLE_DIR, "_build/libdc_oracle.so"], stdout=subprocess.DEVNULL)
     return ORACLE_SO
@@ -531,3 +531,53 @@ def ref_hamming_decode(bits, c, r, eb=0.01):
     lib.hamming_decode.restype = C.c_int
     t = lib.hamming_decode(bits.ctypes.data, cb, int(bits.size), int(r))
     return int(t), bits, cb.raw[:r + 1]
+
+
+# ---- byte-wise codec CT=1 (oracle/dc_oracle_bytewise.c; reference myCompress :3977, myDecompress :3942) ----
+def o_bytewise_compress(x, eb):
+    """-> (array_float[nf], array_char[nc] as uint8, array_char_displacement[nc] int32)"""
+    x = _f32(x)
+    n = x.size
+    af, ac, ad = np.zeros(max(n, 1), np.float32), np.zeros(max(n, 1), np.uint8), np.zeros(max(n, 1), np.int32)
+    lib = oracle()
+    lib.dco_bytewise_compress.restype = C.c_size_t
+    lib.dco_bytewise_compress.argtypes = [C.c_void_p, C.c_size_t, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
+    nf = lib.dco_bytewise_compress(_ptr(x), n, eb, _ptr(af), _ptr(ac), _ptr(ad))
+    return af[:nf].copy(), ac[:n - nf].copy(), ad[:n - nf].copy()
+
+
+def o_bytewise_decompress(af, ac, ad, n):
+    out = np.zeros(max(n, 1), np.float32)
+    af, ac, ad = _f32(af), np.ascontiguousarray(ac, np.uint8), np.ascontiguousarray(ad, np.int32)
+    lib = oracle()
+    lib.dco_bytewise_decompress.restype = None
+    lib.dco_bytewise_decompress.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p]
+    pad = lambda a: a if a.size else np.zeros(1, a.dtype)
+    lib.dco_bytewise_decompress(_ptr(pad(af)), _ptr(pad(ac)), _ptr(pad(ad)), ac.size, n, _ptr(out))
+    return out[:n]
+
+
+def ref_bytewise_compress(x, eb):
+    """The compiled reference's myCompress (impl/dataCompression.c:3977) with absErrorBound = eb."""
+    lib = RefLib(eb).lib
+    x = _f32(x)
+    af, ac, ad = _f32p(), C.c_char_p(), C.POINTER(C.c_int)()
+    lib.myCompress.argtypes = [C.c_void_p, C.POINTER(_f32p), C.POINTER(C.c_char_p), C.POINTER(C.POINTER(C.c_int)), C.c_int]
+    lib.myCompress.restype = C.c_int
+    nf = lib.myCompress(_ptr(x), C.byref(af), C.byref(ac), C.byref(ad), int(x.size))
+    nc = x.size - nf
+    f = np.ctypeslib.as_array(af, (nf,)).copy() if nf else np.zeros(0, np.float32)
+    c = np.frombuffer(C.string_at(ac, nc), np.uint8).copy() if nc else np.zeros(0, np.uint8)
+    d = np.ctypeslib.as_array(ad, (nc,)).copy() if nc else np.zeros(0, np.int32)
+    return f, c, d
+
+
+def ref_bytewise_decompress(af, ac, ad, n, eb):
+    lib = RefLib(eb).lib
+    af = _f32(np.concatenate([af, np.zeros(1, np.float32)]))
+    ac = np.ascontiguousarray(np.concatenate([ac, np.zeros(1, np.uint8)]), np.uint8)
+    ad = np.ascontiguousarray(np.concatenate([ad, np.zeros(1, np.int32)]), np.int32)       # the reference reads one past the end
+    lib.myDecompress.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    lib.myDecompress.restype = _f32p
+    p = lib.myDecompress(_ptr(af), _ptr(ac), _ptr(ad), int(n))
+    return np.ctypeslib.as_array(p, (n,)).copy()
