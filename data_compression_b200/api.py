@@ -31,7 +31,8 @@ EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb",
            "dcb_last_stream_bits", "dcb_gather_face", "dcb_scatter_face", "dcb_himeno_jacobi",
            "dcb_himeno_copy_interior", "dcb_max_stream_bytes_f64", "dcb_workspace_bytes_f64", "dcb_compress_f64",
            "dcb_decompress_f64", "dcb_chunk_stats_f64", "dcb_profile_enable", "dcb_profile_last_ms",
-           "dcb_hm_length", "dcb_hamming_encode", "dcb_hamming_decode"]
+           "dcb_hm_length", "dcb_hamming_encode", "dcb_hamming_decode",
+           "dcb_bytewise_workspace_bytes", "dcb_bytewise_compress", "dcb_bytewise_decompress"]
 
 _lib = None
 
@@ -57,6 +58,12 @@ def lib():
         for f in ("dcb_num_chunks", "dcb_max_stream_bytes", "dcb_workspace_bytes"):
             getattr(L, f).restype = u64
             getattr(L, f).argtypes = [u64, u64]
+        L.dcb_bytewise_workspace_bytes.restype = u64
+        L.dcb_bytewise_workspace_bytes.argtypes = [u64, u64]
+        L.dcb_bytewise_compress.restype = i32
+        L.dcb_bytewise_compress.argtypes = [vp, u64, u64, dbl, vp, vp, vp, vp, vp, u64, vp]
+        L.dcb_bytewise_decompress.restype = i32
+        L.dcb_bytewise_decompress.argtypes = [vp, vp, vp, vp, u64, u64, vp, vp]
         L.dcb_hm_length.restype = i32
         L.dcb_hm_length.argtypes = [i32]
         L.dcb_hamming_encode.restype = i32
@@ -338,6 +345,40 @@ def flip_bits(stream, bit_indices):
     idx = torch.as_tensor(bit_indices, dtype=torch.int64, device=stream.device)
     with torch.cuda.device(stream.device):
         check(lib().dcb_flip_bits(_ptr(stream), _ptr(idx), idx.numel(), _cur_stream(stream.device)), "dcb_flip_bits")
+
+
+def bytewise_compress(x, abs_error_bound=1e-6, chunk_elems=DEFAULT_CHUNK):
+    """myCompress (dataCompression.c:3977) per chunk on the device.  -> dict(array_float, array_char, displacement: fixed-pitch
+    tensors of n entries, chunk c at c*chunk_elems; nfloat[K]; n; chunk_elems; abs_error_bound)"""
+    import torch
+    n = x.numel()
+    K = max(num_chunks(n, chunk_elems), 1)
+    dev = x.device
+    af = torch.zeros(max(n, 1), dtype=torch.float32, device=dev)
+    ac = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
+    ad = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)
+    nf = torch.zeros(K, dtype=torch.int32, device=dev)
+    wsb = lib().dcb_bytewise_workspace_bytes(n, chunk_elems)
+    ws = torch.empty(max(wsb, 256), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().dcb_bytewise_compress(_ptr(x), n, chunk_elems, abs_error_bound, _ptr(af), _ptr(ac), _ptr(ad), _ptr(nf),
+                                          _ptr(ws), wsb, _cur_stream(dev)), "dcb_bytewise_compress")
+    return dict(array_float=af, array_char=ac, displacement=ad, nfloat=nf, n=n, chunk_elems=chunk_elems,
+                abs_error_bound=abs_error_bound)
+
+
+def bytewise_decompress(enc, out=None):
+    """myDecompress (dataCompression.c:3942) per chunk on the device."""
+    import torch
+    n = enc["n"]
+    dev = enc["array_float"].device
+    if out is None:
+        out = torch.empty(n, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().dcb_bytewise_decompress(_ptr(enc["array_float"]), _ptr(enc["array_char"]), _ptr(enc["displacement"]),
+                                            _ptr(enc["nfloat"]), n, enc["chunk_elems"], _ptr(out), _cur_stream(dev)),
+              "dcb_bytewise_decompress")
+    return out
 
 
 def hm_length(k):

@@ -19,6 +19,7 @@
 #include "dcb_face.cuh"
 #include "dcb_f64.cuh"
 #include "dcb_hamming.cuh"
+#include "dcb_bytewise.cuh"
 static int ensure_crc_tables(cudaStream_t st);
 #include <math.h>
 #include <stdio.h>
@@ -751,6 +752,56 @@ extern "C" int dcb_debug_timeline(long long* host_dst) {
   return DCB_OK;
 }
 #endif
+
+// ---- byte-wise codec CT=1 (myCompress / myDecompress) ---------------------------------------------------------------------
+static uint64_t bw_tiles(uint64_t n) { return (n + DCB_BW_NT - 1) / DCB_BW_NT; }
+static uint64_t bw_flags_bytes(uint64_t n) { return (n + 255) & ~(uint64_t)255; }
+extern "C" uint64_t dcb_bytewise_workspace_bytes(uint64_t n, uint64_t chunk) {
+  return bw_flags_bytes(n) + 4 * bw_tiles(n) + 4 * dcb_num_chunks(n, chunk) + 256;
+}
+extern "C" int dcb_bytewise_compress(const float* d_in, uint64_t n, uint64_t chunk, double eb, float* d_float, uint8_t* d_char,
+                                     int32_t* d_disp, uint32_t* d_chunk_nfloat, void* d_ws, uint64_t ws_bytes, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  cudaStream_t st = (cudaStream_t)stream;
+  CodecConst k;
+  if (make_const(eb, &k) != DCB_OK) return DCB_EINVAL;
+  if (n == 0) return DCB_OK;
+  const bool single = single_chunk(n, chunk);
+  if (!single && (chunk % DCB_TILE) != 0) return DCB_EINVAL;
+  if (!d_in || !d_float || !d_char || !d_disp || !d_chunk_nfloat || n >= (1ull << 40) || (single && n >= (1ull << 31))) return DCB_EINVAL;
+  if (!d_ws || ws_bytes < dcb_bytewise_workspace_bytes(n, chunk)) return DCB_ECAPACITY;
+  const uint64_t K = dcb_num_chunks(n, chunk);
+  BwArgs a;
+  a.in = d_in; a.n = n; a.chunk = single ? n : chunk; a.tp = k.tp;
+  a.flags = (uint8_t*)d_ws;
+  a.tile_hits = (uint32_t*)((char*)d_ws + bw_flags_bytes(n));
+  a.chunk_slow = a.tile_hits + bw_tiles(n);
+  a.chunk_nfloat = d_chunk_nfloat; a.af = d_float; a.ac = d_char; a.ad = d_disp;
+  CK(cudaMemsetAsync(a.chunk_slow, 0, 4 * K, st));
+  dcb_bw_classify_kernel<<<(unsigned)bw_tiles(n), DCB_BW_NT, 0, st>>>(a);
+  CK(cudaGetLastError());
+  dcb_bw_slow_kernel<<<(unsigned)((K + 63) / 64), 64, 0, st>>>(a, K);
+  CK(cudaGetLastError());
+  dcb_bw_offsets_kernel<<<(unsigned)K, DCB_BW_NT, 0, st>>>(a);
+  CK(cudaGetLastError());
+  dcb_bw_scatter_kernel<<<(unsigned)bw_tiles(n), DCB_BW_NT, 0, st>>>(a);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+extern "C" int dcb_bytewise_decompress(const float* d_float, const uint8_t* d_char, const int32_t* d_disp,
+                                       const uint32_t* d_chunk_nfloat, uint64_t n, uint64_t chunk, float* d_out, void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  if (n == 0) return DCB_OK;
+  const bool single = single_chunk(n, chunk);
+  if (!single && (chunk % DCB_TILE) != 0) return DCB_EINVAL;
+  if (!d_float || !d_char || !d_disp || !d_chunk_nfloat || !d_out || (single && n >= (1ull << 31))) return DCB_EINVAL;
+  BwDecArgs a;
+  a.af = d_float; a.ac = d_char; a.ad = d_disp; a.chunk_nfloat = d_chunk_nfloat; a.n = n; a.chunk = single ? n : chunk;
+  a.K = dcb_num_chunks(n, chunk); a.out = d_out;
+  dcb_bw_decode_kernel<<<(unsigned)((a.K + 63) / 64), 64, 0, (cudaStream_t)stream>>>(a);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
 
 // ---- Hamming SECDED over blocks of the finished stream (CT=10) ------------------------------------------------------------
 extern "C" int dcb_hm_length(int k) { return k < 0 ? -1 : hm_length(k); }

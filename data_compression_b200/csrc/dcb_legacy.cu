@@ -443,3 +443,62 @@ extern "C" int hamming_decode(unsigned char* bits, char* c, int bytes, int r) { 
   for (int i = 0; i <= r; i++) c[i] = (char)('0' + ((fixed >> i) & 1u));
   return et;
 }
+
+
+// ---- CT=1: the byte-wise codec (dataCompression.h: myCompress / myDecompress, float) ------------------------------------------
+#define BW_CK(call) do { if ((call) != cudaSuccess) die("bytewise: " #call, DCB_ECUDA); } while (0)
+extern "C" int myCompress(float data[], float** array_float, char** array_char, int** array_char_displacement, int num) {   // :3977
+  if (dcb_device_count() == 0) die("myCompress", DCB_ENODEVICE);
+  if (num <= 0) return 0;
+  const uint64_t n = (uint64_t)num;
+  float *d_in, *d_f; uint8_t* d_c; int32_t* d_d; uint32_t* d_nf; void* d_ws;
+  const uint64_t wsb = dcb_bytewise_workspace_bytes(n, 0);
+  BW_CK(cudaMalloc(&d_in, n * 4)); BW_CK(cudaMalloc(&d_f, n * 4)); BW_CK(cudaMalloc(&d_c, n)); BW_CK(cudaMalloc(&d_d, n * 4));
+  BW_CK(cudaMalloc(&d_nf, 4)); BW_CK(cudaMalloc(&d_ws, wsb));
+  BW_CK(cudaMemcpy(d_in, data, n * 4, cudaMemcpyHostToDevice));
+  const int rc = dcb_bytewise_compress(d_in, n, 0, dc_get_abs_error_bound(), d_f, d_c, d_d, d_nf, d_ws, wsb, nullptr);
+  if (rc) die("myCompress", rc);
+  uint32_t nf = 0;
+  BW_CK(cudaMemcpy(&nf, d_nf, 4, cudaMemcpyDeviceToHost));
+  const uint32_t nc = (uint32_t)num - nf;
+  // the reference grows the caller's arrays with realloc (callers start from NULL) and leaves them untouched when empty
+  if (nf) {
+    float* f = (float*)realloc(*array_float, sizeof(float) * nf);
+    if (!f) { free(*array_float); printf("Error (re)allocating memory\n"); exit(1); }                 // :4001-4005
+    BW_CK(cudaMemcpy(f, d_f, (size_t)nf * 4, cudaMemcpyDeviceToHost));
+    *array_float = f;
+  }
+  if (nc) {
+    char* c = (char*)realloc(*array_char, sizeof(char) * nc);
+    int* d = (int*)realloc(*array_char_displacement, sizeof(int) * nc);
+    if (!c || !d) { printf("Error (re)allocating memory\n"); exit(1); }                                // :4081-4086
+    BW_CK(cudaMemcpy(c, d_c, nc, cudaMemcpyDeviceToHost));
+    BW_CK(cudaMemcpy(d, d_d, (size_t)nc * 4, cudaMemcpyDeviceToHost));
+    *array_char = c; *array_char_displacement = d;
+  }
+  cudaFree(d_in); cudaFree(d_f); cudaFree(d_c); cudaFree(d_d); cudaFree(d_nf); cudaFree(d_ws);
+  return (int)nf;
+}
+extern "C" float* myDecompress(float array_float[], char array_char[], int array_char_displacement[], int num) {           // :3942
+  if (dcb_device_count() == 0) die("myDecompress", DCB_ENODEVICE);
+  float* out = (float*)malloc(sizeof(float) * (size_t)(num > 0 ? num : 1));
+  if (num <= 0) return out;
+  // The call does not say how many hits there are: the reference finds out by comparing displacement[p] - 1 with the running
+  // index (and reads displacement[p] one past its end once the last hit is consumed, :3948).  The same walk, the same reads.
+  uint32_t nc = 0;
+  if (array_char_displacement)
+    for (int i = 0; i < num; i++)
+      if (array_char_displacement[nc] - 1 == i) nc++;
+  const uint32_t nf = (uint32_t)num - nc;
+  const uint64_t n = (uint64_t)num;
+  float *d_f, *d_o; uint8_t* d_c; int32_t* d_d; uint32_t* d_nf;
+  BW_CK(cudaMalloc(&d_f, n * 4)); BW_CK(cudaMalloc(&d_o, n * 4)); BW_CK(cudaMalloc(&d_c, n)); BW_CK(cudaMalloc(&d_d, n * 4)); BW_CK(cudaMalloc(&d_nf, 4));
+  if (nf) BW_CK(cudaMemcpy(d_f, array_float, (size_t)nf * 4, cudaMemcpyHostToDevice));
+  if (nc) { BW_CK(cudaMemcpy(d_c, array_char, nc, cudaMemcpyHostToDevice)); BW_CK(cudaMemcpy(d_d, array_char_displacement, (size_t)nc * 4, cudaMemcpyHostToDevice)); }
+  BW_CK(cudaMemcpy(d_nf, &nf, 4, cudaMemcpyHostToDevice));
+  const int rc = dcb_bytewise_decompress(d_f, d_c, d_d, d_nf, n, 0, d_o, nullptr);
+  if (rc) die("myDecompress", rc);
+  BW_CK(cudaMemcpy(out, d_o, n * 4, cudaMemcpyDeviceToHost));
+  cudaFree(d_f); cudaFree(d_o); cudaFree(d_c); cudaFree(d_d); cudaFree(d_nf);
+  return out;
+}

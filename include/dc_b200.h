@@ -100,6 +100,17 @@ int dcb_chunk_medium(const float* d_in, uint64_t n, float* d_medium, int32_t* d_
 /* bit_flip (dataCompression.c:5858) test hook: flips bit (7 - bit_index%8) of byte bit_index/8 for each index */
 int dcb_flip_bits(uint8_t* d_stream, const uint64_t* d_bit_indices, uint64_t count, void* cuda_stream);
 
+/* ---- byte-wise codec CT=1: myCompress (dataCompression.c:3977) / myDecompress (:3942), one reference call
+ * per chunk.  Fixed-pitch outputs: chunk c owns elements [c*chunk_elems, ...) of d_float (its raw floats, d_chunk_nfloat[c] of
+ * them), d_char (hit types 'a'..'d') and d_disp (their 1-based positions inside the chunk); hits = chunk length - raw floats.
+ * chunk_elems = 0: one chunk = the whole array (the legacy call). */
+uint64_t dcb_bytewise_workspace_bytes(uint64_t n, uint64_t chunk_elems);
+int dcb_bytewise_compress(const float* d_in, uint64_t n, uint64_t chunk_elems, double abs_error_bound, float* d_float,
+                          uint8_t* d_char, int32_t* d_disp, uint32_t* d_chunk_nfloat, void* d_workspace,
+                          uint64_t workspace_bytes, void* cuda_stream);
+int dcb_bytewise_decompress(const float* d_float, const uint8_t* d_char, const int32_t* d_disp, const uint32_t* d_chunk_nfloat,
+                            uint64_t n, uint64_t chunk_elems, float* d_out, void* cuda_stream);
+
 /* ---- Hamming SECDED of CT=10: hamming_encode / hamming_decode (dataCompression.c:5742, :5752), one
  * call per block of the finished stream as impl/pingpong.c:296-311 / :487-505 make them.  Block b covers bytes
  * [b*block_bytes, min(total_bytes, (b+1)*block_bytes)); its r = dcb_hm_length(8 * its bytes) check bits c[0..r-1] and the
