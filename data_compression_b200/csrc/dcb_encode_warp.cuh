@@ -469,13 +469,19 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
           all3 = false;
           #pragma unroll
           for (int e = 0; e < DCB_E; e++) {
-            const uint32_t f = (CT == CT_NP || ((miss >> e) & 1u)) ? 0u : C48_FIELD(chi, clo, e);
             uint32_t ft; int fl;
             fallback_top<CT, true>(f2u(x[e]), a.k, type, mask17, ft, fl);
-            code[e] = f ? (f << 29) : ft;
-            len[e] = f ? 3 : fl;
-            if (e >= vcnt) { code[e] = 0u; len[e] = 0; }
+            // the element's 3-bit field, top aligned, straight from the 48-bit string
+            const uint32_t f3 = (e < 10 ? (chi << (3 * e)) : (e == 10 ? ((chi << 30) | (clo >> 2)) : (clo << (3 * e - 32)))) & 0xE0000000u;
+            const bool ms = (CT == CT_NP) || ((miss >> e) & 1u);
+            code[e] = ms ? ft : f3;
+            len[e] = ms ? fl : 3;
             total += (uint32_t)len[e];
+          }
+          if (cbase + (uint64_t)(j + 1) * DCB_WR > cend) {     // warp-uniform: a ragged round, padding carries no code
+            #pragma unroll
+            for (int e = 0; e < DCB_E; e++)
+              if (e >= vcnt) { total -= (uint32_t)len[e]; code[e] = 0u; len[e] = 0; }
           }
         }
       } else {
