@@ -49,6 +49,16 @@ def test_host_logic(L):
     assert L.dcb_workspace_bytes(1 << 20, 4096) >= 8 * 256
 
 
+def test_host_logic_of_the_widened_rows(L):
+    # hmLength (dataCompression.c:5587): smallest r with 2^r - 1 - r - k >= 0
+    assert [L.dcb_hm_length(k) for k in (1, 4, 11, 12, 1000000)] == [2, 3, 4, 5, 20]
+    # slot path: one 16 KB slot per chunk on top of the tables; multi-tile chunks keep the small workspace
+    n = 1 << 20
+    assert L.dcb_workspace_bytes(n, 4096) >= (n // 4096) * 16384
+    assert L.dcb_workspace_bytes(n, 8192) < 1 << 16
+    assert L.dcb_bytewise_workspace_bytes(n, 4096) >= n
+
+
 def test_no_silent_cpu_fallback(L):
     import torch
     if torch.cuda.is_available():
@@ -59,6 +69,10 @@ def test_no_silent_cpu_fallback(L):
         api.compress_host(x, ct=5, abs_error_bound=0.01)
     with pytest.raises(api.DcbError):
         api.compress(torch.zeros(16), ct=5)
+    buf = np.zeros(64, np.uint8)
+    chk = np.zeros(1, np.uint32)
+    assert L.dcb_hamming_encode(buf.ctypes.data, 64, 64, chk.ctypes.data, None, None) == -4          # DCB_ENODEVICE
+    assert L.dcb_bytewise_decompress(buf.ctypes.data, buf.ctypes.data, buf.ctypes.data, chk.ctypes.data, 4, 0, buf.ctypes.data, None) == -4
 
 
 def test_product_does_not_import_oracle():
