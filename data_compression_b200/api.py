@@ -32,7 +32,8 @@ EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb",
            "dcb_himeno_copy_interior", "dcb_max_stream_bytes_f64", "dcb_workspace_bytes_f64", "dcb_compress_f64",
            "dcb_decompress_f64", "dcb_chunk_stats_f64", "dcb_profile_enable", "dcb_profile_last_ms",
            "dcb_hm_length", "dcb_hamming_encode", "dcb_hamming_decode",
-           "dcb_bytewise_workspace_bytes", "dcb_bytewise_compress", "dcb_bytewise_decompress"]
+           "dcb_bytewise_workspace_bytes", "dcb_bytewise_compress", "dcb_bytewise_decompress",
+           "dcb_bytewise_compress_f64", "dcb_bytewise_decompress_f64"]
 
 _lib = None
 
@@ -64,6 +65,10 @@ def lib():
         L.dcb_bytewise_compress.argtypes = [vp, u64, u64, dbl, vp, vp, vp, vp, vp, u64, vp]
         L.dcb_bytewise_decompress.restype = i32
         L.dcb_bytewise_decompress.argtypes = [vp, vp, vp, vp, u64, u64, vp, vp]
+        L.dcb_bytewise_compress_f64.restype = i32
+        L.dcb_bytewise_compress_f64.argtypes = [vp, u64, u64, dbl, vp, vp, vp, vp, vp, u64, vp]
+        L.dcb_bytewise_decompress_f64.restype = i32
+        L.dcb_bytewise_decompress_f64.argtypes = [vp, vp, vp, vp, u64, u64, vp, vp]
         L.dcb_hm_length.restype = i32
         L.dcb_hm_length.argtypes = [i32]
         L.dcb_hamming_encode.restype = i32
@@ -354,15 +359,17 @@ def bytewise_compress(x, abs_error_bound=1e-6, chunk_elems=DEFAULT_CHUNK):
     n = x.numel()
     K = max(num_chunks(n, chunk_elems), 1)
     dev = x.device
-    af = torch.zeros(max(n, 1), dtype=torch.float32, device=dev)
+    f64 = x.dtype == torch.float64
+    af = torch.zeros(max(n, 1), dtype=x.dtype, device=dev)
     ac = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
     ad = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)
     nf = torch.zeros(K, dtype=torch.int32, device=dev)
     wsb = lib().dcb_bytewise_workspace_bytes(n, chunk_elems)
     ws = torch.empty(max(wsb, 256), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        check(lib().dcb_bytewise_compress(_ptr(x), n, chunk_elems, abs_error_bound, _ptr(af), _ptr(ac), _ptr(ad), _ptr(nf),
-                                          _ptr(ws), wsb, _cur_stream(dev)), "dcb_bytewise_compress")
+        fn = lib().dcb_bytewise_compress_f64 if f64 else lib().dcb_bytewise_compress
+        check(fn(_ptr(x), n, chunk_elems, abs_error_bound, _ptr(af), _ptr(ac), _ptr(ad), _ptr(nf), _ptr(ws), wsb,
+                 _cur_stream(dev)), "dcb_bytewise_compress")
     return dict(array_float=af, array_char=ac, displacement=ad, nfloat=nf, n=n, chunk_elems=chunk_elems,
                 abs_error_bound=abs_error_bound)
 
@@ -372,12 +379,13 @@ def bytewise_decompress(enc, out=None):
     import torch
     n = enc["n"]
     dev = enc["array_float"].device
+    f64 = enc["array_float"].dtype == torch.float64
     if out is None:
-        out = torch.empty(n, dtype=torch.float32, device=dev)
+        out = torch.empty(n, dtype=enc["array_float"].dtype, device=dev)
     with torch.cuda.device(dev):
-        check(lib().dcb_bytewise_decompress(_ptr(enc["array_float"]), _ptr(enc["array_char"]), _ptr(enc["displacement"]),
-                                            _ptr(enc["nfloat"]), n, enc["chunk_elems"], _ptr(out), _cur_stream(dev)),
-              "dcb_bytewise_decompress")
+        fn = lib().dcb_bytewise_decompress_f64 if f64 else lib().dcb_bytewise_decompress
+        check(fn(_ptr(enc["array_float"]), _ptr(enc["array_char"]), _ptr(enc["displacement"]), _ptr(enc["nfloat"]), n,
+                 enc["chunk_elems"], _ptr(out), _cur_stream(dev)), "dcb_bytewise_decompress")
     return out
 
 

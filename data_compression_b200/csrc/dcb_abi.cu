@@ -759,8 +759,9 @@ static uint64_t bw_flags_bytes(uint64_t n) { return (n + 255) & ~(uint64_t)255; 
 extern "C" uint64_t dcb_bytewise_workspace_bytes(uint64_t n, uint64_t chunk) {
   return bw_flags_bytes(n) + 4 * bw_tiles(n) + 4 * dcb_num_chunks(n, chunk) + 256;
 }
-extern "C" int dcb_bytewise_compress(const float* d_in, uint64_t n, uint64_t chunk, double eb, float* d_float, uint8_t* d_char,
-                                     int32_t* d_disp, uint32_t* d_chunk_nfloat, void* d_ws, uint64_t ws_bytes, void* stream) {
+template <typename T>
+static int bytewise_compress_t(const T* d_in, uint64_t n, uint64_t chunk, double eb, T* d_val, uint8_t* d_char, int32_t* d_disp,
+                               uint32_t* d_chunk_nval, void* d_ws, uint64_t ws_bytes, void* stream) {
   if (dcb_device_count() == 0) return DCB_ENODEVICE;
   cudaStream_t st = (cudaStream_t)stream;
   CodecConst k;
@@ -768,39 +769,57 @@ extern "C" int dcb_bytewise_compress(const float* d_in, uint64_t n, uint64_t chu
   if (n == 0) return DCB_OK;
   const bool single = single_chunk(n, chunk);
   if (!single && (chunk % DCB_TILE) != 0) return DCB_EINVAL;
-  if (!d_in || !d_float || !d_char || !d_disp || !d_chunk_nfloat || n >= (1ull << 40) || (single && n >= (1ull << 31))) return DCB_EINVAL;
+  if (!d_in || !d_val || !d_char || !d_disp || !d_chunk_nval || n >= (1ull << 40) || (single && n >= (1ull << 31))) return DCB_EINVAL;
   if (!d_ws || ws_bytes < dcb_bytewise_workspace_bytes(n, chunk)) return DCB_ECAPACITY;
   const uint64_t K = dcb_num_chunks(n, chunk);
-  BwArgs a;
-  a.in = d_in; a.n = n; a.chunk = single ? n : chunk; a.tp = k.tp;
+  BwArgs<T> a;
+  a.in = d_in; a.n = n; a.chunk = single ? n : chunk;
+  a.tp = sizeof(T) == 4 ? (T)k.tp : (T)eb;              // float32: diff_min (float) <= absErrorBound (double), folded into a float threshold
   a.flags = (uint8_t*)d_ws;
   a.tile_hits = (uint32_t*)((char*)d_ws + bw_flags_bytes(n));
   a.chunk_slow = a.tile_hits + bw_tiles(n);
-  a.chunk_nfloat = d_chunk_nfloat; a.af = d_float; a.ac = d_char; a.ad = d_disp;
+  a.chunk_nfloat = d_chunk_nval; a.af = d_val; a.ac = d_char; a.ad = d_disp;
   CK(cudaMemsetAsync(a.chunk_slow, 0, 4 * K, st));
-  dcb_bw_classify_kernel<<<(unsigned)bw_tiles(n), DCB_BW_NT, 0, st>>>(a);
+  dcb_bw_classify_kernel<T><<<(unsigned)bw_tiles(n), DCB_BW_NT, 0, st>>>(a);
   CK(cudaGetLastError());
-  dcb_bw_slow_kernel<<<(unsigned)((K + 63) / 64), 64, 0, st>>>(a, K);
+  dcb_bw_slow_kernel<T><<<(unsigned)((K + 63) / 64), 64, 0, st>>>(a, K);
   CK(cudaGetLastError());
-  dcb_bw_offsets_kernel<<<(unsigned)K, DCB_BW_NT, 0, st>>>(a);
+  dcb_bw_offsets_kernel<T><<<(unsigned)K, DCB_BW_NT, 0, st>>>(a);
   CK(cudaGetLastError());
-  dcb_bw_scatter_kernel<<<(unsigned)bw_tiles(n), DCB_BW_NT, 0, st>>>(a);
+  dcb_bw_scatter_kernel<T><<<(unsigned)bw_tiles(n), DCB_BW_NT, 0, st>>>(a);
   CK(cudaGetLastError());
   return DCB_OK;
 }
-extern "C" int dcb_bytewise_decompress(const float* d_float, const uint8_t* d_char, const int32_t* d_disp,
-                                       const uint32_t* d_chunk_nfloat, uint64_t n, uint64_t chunk, float* d_out, void* stream) {
+template <typename T>
+static int bytewise_decompress_t(const T* d_val, const uint8_t* d_char, const int32_t* d_disp, const uint32_t* d_chunk_nval,
+                                 uint64_t n, uint64_t chunk, T* d_out, void* stream) {
   if (dcb_device_count() == 0) return DCB_ENODEVICE;
   if (n == 0) return DCB_OK;
   const bool single = single_chunk(n, chunk);
   if (!single && (chunk % DCB_TILE) != 0) return DCB_EINVAL;
-  if (!d_float || !d_char || !d_disp || !d_chunk_nfloat || !d_out || (single && n >= (1ull << 31))) return DCB_EINVAL;
-  BwDecArgs a;
-  a.af = d_float; a.ac = d_char; a.ad = d_disp; a.chunk_nfloat = d_chunk_nfloat; a.n = n; a.chunk = single ? n : chunk;
+  if (!d_val || !d_char || !d_disp || !d_chunk_nval || !d_out || (single && n >= (1ull << 31))) return DCB_EINVAL;
+  BwDecArgs<T> a;
+  a.af = d_val; a.ac = d_char; a.ad = d_disp; a.chunk_nfloat = d_chunk_nval; a.n = n; a.chunk = single ? n : chunk;
   a.K = dcb_num_chunks(n, chunk); a.out = d_out;
-  dcb_bw_decode_kernel<<<(unsigned)((a.K + 63) / 64), 64, 0, (cudaStream_t)stream>>>(a);
+  dcb_bw_decode_kernel<T><<<(unsigned)((a.K + 63) / 64), 64, 0, (cudaStream_t)stream>>>(a);
   CK(cudaGetLastError());
   return DCB_OK;
+}
+extern "C" int dcb_bytewise_compress(const float* d_in, uint64_t n, uint64_t chunk, double eb, float* d_float, uint8_t* d_char,
+                                     int32_t* d_disp, uint32_t* d_chunk_nfloat, void* d_ws, uint64_t ws_bytes, void* stream) {
+  return bytewise_compress_t<float>(d_in, n, chunk, eb, d_float, d_char, d_disp, d_chunk_nfloat, d_ws, ws_bytes, stream);
+}
+extern "C" int dcb_bytewise_decompress(const float* d_float, const uint8_t* d_char, const int32_t* d_disp,
+                                       const uint32_t* d_chunk_nfloat, uint64_t n, uint64_t chunk, float* d_out, void* stream) {
+  return bytewise_decompress_t<float>(d_float, d_char, d_disp, d_chunk_nfloat, n, chunk, d_out, stream);
+}
+extern "C" int dcb_bytewise_compress_f64(const double* d_in, uint64_t n, uint64_t chunk, double eb, double* d_double, uint8_t* d_char,
+                                         int32_t* d_disp, uint32_t* d_chunk_ndouble, void* d_ws, uint64_t ws_bytes, void* stream) {
+  return bytewise_compress_t<double>(d_in, n, chunk, eb, d_double, d_char, d_disp, d_chunk_ndouble, d_ws, ws_bytes, stream);
+}
+extern "C" int dcb_bytewise_decompress_f64(const double* d_double, const uint8_t* d_char, const int32_t* d_disp,
+                                           const uint32_t* d_chunk_ndouble, uint64_t n, uint64_t chunk, double* d_out, void* stream) {
+  return bytewise_decompress_t<double>(d_double, d_char, d_disp, d_chunk_ndouble, n, chunk, d_out, stream);
 }
 
 // ---- Hamming SECDED over blocks of the finished stream (CT=10) ------------------------------------------------------------

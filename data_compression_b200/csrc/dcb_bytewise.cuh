@@ -15,37 +15,56 @@
 
 #define DCB_BW_NT 256
 
+// every operation rounded on its own, never contracted; float32 (myCompress :3977) and float64 (myCompress_double :3815)
+template <typename T> struct BwFp;
+template <> struct BwFp<float> {
+  static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+  static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+  static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+  static __device__ __forceinline__ float abs(float a) { return fabsf(a); }
+};
+template <> struct BwFp<double> {
+  static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
+  static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+  static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+  static __device__ __forceinline__ double abs(double a) { return fabs(a); }
+};
+
+template <typename T>
 struct BwArgs {
-  const float* in; uint64_t n; uint64_t chunk;          // chunk: elements per chunk (multiple of 256) or n for a single chunk
-  float tp;                                             // largest float <= absErrorBound (diff_min <= absErrorBound in double, :4068)
+  const T* in; uint64_t n; uint64_t chunk;              // chunk: elements per chunk (multiple of 256) or n for a single chunk
+  T tp;                                                 // float32: largest float <= absErrorBound (the compare is in double, :4068); float64: the bound
   uint8_t* flags;                                       // [n]
   uint32_t* tile_hits;                                  // [tiles]  hits per tile, then (offsets pass) exclusive prefix inside the chunk
   uint32_t* chunk_slow;                                 // [K]
   uint32_t* chunk_nfloat;                               // [K]
-  float* af; uint8_t* ac; int32_t* ad;                  // [n] each, fixed pitch per chunk
+  T* af; uint8_t* ac; int32_t* ad;                      // [n] each, fixed pitch per chunk
 };
 
-__device__ __forceinline__ uint8_t bw_classify(float b1, float b2, float b3, float b4, float v, float tp) {
-  const float p2 = __fsub_rn(__fmul_rn(2.0f, b1), b2);                                     // :4031
-  const float p3 = __fadd_rn(__fsub_rn(__fmul_rn(3.0f, b1), __fmul_rn(3.0f, b2)), b3);      // :4032
-  const float p4 = __fsub_rn(__fadd_rn(__fsub_rn(__fmul_rn(4.0f, b1), __fmul_rn(6.0f, b2)), __fmul_rn(4.0f, b3)), b4);   // :4033
-  const float d1 = fabsf(__fsub_rn(b1, v)), d2 = fabsf(__fsub_rn(p2, v)), d3 = fabsf(__fsub_rn(p3, v)), d4 = fabsf(__fsub_rn(p4, v));
-  float dm = d1; uint8_t t = 'a';
+template <typename T>
+__device__ __forceinline__ uint8_t bw_classify(T b1, T b2, T b3, T b4, T v, T tp) {
+  typedef BwFp<T> F;
+  const T p2 = F::sub(F::mul((T)2, b1), b2);                                                // :4031
+  const T p3 = F::add(F::sub(F::mul((T)3, b1), F::mul((T)3, b2)), b3);                       // :4032
+  const T p4 = F::sub(F::add(F::sub(F::mul((T)4, b1), F::mul((T)6, b2)), F::mul((T)4, b3)), b4);   // :4033
+  const T d1 = F::abs(F::sub(b1, v)), d2 = F::abs(F::sub(p2, v)), d3 = F::abs(F::sub(p3, v)), d4 = F::abs(F::sub(p4, v));
+  T dm = d1; uint8_t t = 'a';
   if (d2 < dm) { dm = d2; t = 'b'; }                                                       // strict '<': NaN never wins (:4041-4058)
   if (d3 < dm) { dm = d3; t = 'c'; }
   if (d4 < dm) { dm = d4; t = 'd'; }
   return (dm <= tp) ? t : (uint8_t)0;
 }
 
-__global__ void __launch_bounds__(DCB_BW_NT) dcb_bw_classify_kernel(const BwArgs a) {
+template <typename T>
+__global__ void __launch_bounds__(DCB_BW_NT) dcb_bw_classify_kernel(const BwArgs<T> a) {
   const uint64_t i = (uint64_t)blockIdx.x * DCB_BW_NT + threadIdx.x;
   uint8_t f = 0; bool marker = false;
   uint64_t c = 0;
   if (i < a.n) {
     c = i / a.chunk;
     const uint64_t r = i - c * a.chunk;                 // index inside the chunk
-    const float v = __ldg(a.in + i);
-    marker = (v == -1.0f);
+    const T v = __ldg(a.in + i);
+    marker = (v == (T)-1);
     if (r >= 4) f = bw_classify(__ldg(a.in + i - 1), __ldg(a.in + i - 2), __ldg(a.in + i - 3), __ldg(a.in + i - 4), v, a.tp);
     a.flags[i] = f;
   }
@@ -58,17 +77,19 @@ __global__ void __launch_bounds__(DCB_BW_NT) dcb_bw_classify_kernel(const BwArgs
 }
 
 // chunks that contain -1.0f: the reference's state machine, one thread per chunk (flags and tile counts rewritten)
-__global__ void dcb_bw_slow_kernel(const BwArgs a, uint64_t K) {
+template <typename T>
+__global__ void dcb_bw_slow_kernel(const BwArgs<T> a, uint64_t K) {
   const uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= K || !a.chunk_slow[c]) return;
   const uint64_t base = c * a.chunk, nc = min(a.chunk, a.n - base);
-  float b1 = -1.0f, b2 = -1.0f, b3 = -1.0f, b4 = -1.0f;
+  const T M = (T)-1;
+  T b1 = M, b2 = M, b3 = M, b4 = M;
   uint32_t hits = 0;
   for (uint64_t r = 0; r < nc; r++) {
-    const float v = a.in[base + r];
+    const T v = a.in[base + r];
     uint8_t f = 0;
-    if (b4 == -1.0f || b3 == -1.0f || b2 == -1.0f || b1 == -1.0f) {                       // :3996-4027
-      if (b4 == -1.0f) b4 = v; else if (b3 == -1.0f) b3 = v; else if (b2 == -1.0f) b2 = v; else b1 = v;
+    if (b4 == M || b3 == M || b2 == M || b1 == M) {                                       // :3996-4027
+      if (b4 == M) b4 = v; else if (b3 == M) b3 = v; else if (b2 == M) b2 = v; else b1 = v;
     } else {
       f = bw_classify(b1, b2, b3, b4, v, a.tp);
       b4 = b3; b3 = b2; b2 = b1; b1 = v;
@@ -80,7 +101,8 @@ __global__ void dcb_bw_slow_kernel(const BwArgs a, uint64_t K) {
 }
 
 // one block per chunk: tile_hits -> exclusive prefix inside the chunk; raw-float count of the chunk
-__global__ void __launch_bounds__(DCB_BW_NT) dcb_bw_offsets_kernel(const BwArgs a) {
+template <typename T>
+__global__ void __launch_bounds__(DCB_BW_NT) dcb_bw_offsets_kernel(const BwArgs<T> a) {
   __shared__ uint32_t s_w[DCB_BW_NT / 32];
   __shared__ uint32_t s_run;
   const uint64_t c = blockIdx.x;
@@ -108,7 +130,8 @@ __global__ void __launch_bounds__(DCB_BW_NT) dcb_bw_offsets_kernel(const BwArgs 
   if (threadIdx.x == 0) a.chunk_nfloat[c] = (uint32_t)nc - s_run;
 }
 
-__global__ void __launch_bounds__(DCB_BW_NT) dcb_bw_scatter_kernel(const BwArgs a) {
+template <typename T>
+__global__ void __launch_bounds__(DCB_BW_NT) dcb_bw_scatter_kernel(const BwArgs<T> a) {
   __shared__ uint32_t s_w[DCB_BW_NT / 32];
   const uint64_t i = (uint64_t)blockIdx.x * DCB_BW_NT + threadIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -125,30 +148,33 @@ __global__ void __launch_bounds__(DCB_BW_NT) dcb_bw_scatter_kernel(const BwArgs 
   else a.af[base + (r - before)] = __ldg(a.in + i);
 }
 
+template <typename T>
 struct BwDecArgs {
-  const float* af; const uint8_t* ac; const int32_t* ad; const uint32_t* chunk_nfloat;
-  uint64_t n; uint64_t chunk; uint64_t K; float* out;
+  const T* af; const uint8_t* ac; const int32_t* ad; const uint32_t* chunk_nfloat;
+  uint64_t n; uint64_t chunk; uint64_t K; T* out;
 };
 // myDecompress :3942-3975: closed loop on the reconstructed values, one thread per chunk
-__global__ void dcb_bw_decode_kernel(const BwDecArgs a) {
+template <typename T>
+__global__ void dcb_bw_decode_kernel(const BwDecArgs<T> a) {
+  typedef BwFp<T> F;
   const uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= a.K) return;
   const uint64_t base = c * a.chunk, nc = min(a.chunk, a.n - base);
   const uint32_t nhit = (uint32_t)nc - a.chunk_nfloat[c];
-  const float* af = a.af + base; const uint8_t* ac = a.ac + base; const int32_t* ad = a.ad + base;
-  float* out = a.out + base;
+  const T* af = a.af + base; const uint8_t* ac = a.ac + base; const int32_t* ad = a.ad + base;
+  T* out = a.out + base;
   uint32_t fp = 0, cp = 0;
-  float o1 = 0.0f, o2 = 0.0f, o3 = 0.0f, o4 = 0.0f;
+  T o1 = 0, o2 = 0, o3 = 0, o4 = 0;
   int32_t next = nhit ? ad[0] - 1 : -1;
   for (uint32_t r = 0; r < (uint32_t)nc; r++) {
-    float v;
+    T v;
     if ((int32_t)r == next) {
       const uint8_t t = ac[cp++];
-      v = 0.0f;
+      v = 0;
       if (t == 'a') v = o1;
-      else if (t == 'b') v = __fsub_rn(__fmul_rn(2.0f, o1), o2);
-      else if (t == 'c') v = __fadd_rn(__fsub_rn(__fmul_rn(3.0f, o1), __fmul_rn(3.0f, o2)), o3);
-      else if (t == 'd') v = __fsub_rn(__fadd_rn(__fsub_rn(__fmul_rn(4.0f, o1), __fmul_rn(6.0f, o2)), __fmul_rn(4.0f, o3)), o4);
+      else if (t == 'b') v = F::sub(F::mul((T)2, o1), o2);
+      else if (t == 'c') v = F::add(F::sub(F::mul((T)3, o1), F::mul((T)3, o2)), o3);
+      else if (t == 'd') v = F::sub(F::add(F::sub(F::mul((T)4, o1), F::mul((T)6, o2)), F::mul((T)4, o3)), o4);
       next = (cp < nhit) ? ad[cp] - 1 : -1;
     } else {
       v = af[fp++];

@@ -502,3 +502,58 @@ extern "C" float* myDecompress(float array_float[], char array_char[], int array
   cudaFree(d_f); cudaFree(d_o); cudaFree(d_c); cudaFree(d_d); cudaFree(d_nf);
   return out;
 }
+
+
+// ---- CT=1, float64: myCompress_double / myDecompress_double (the k-means / MM / LU callers) -----------------------------------
+extern "C" int myCompress_double(double data[], double** array_double, char** array_char, int** array_char_displacement, int num) {   // :3815
+  if (dcb_device_count() == 0) die("myCompress_double", DCB_ENODEVICE);
+  if (num <= 0) return 0;
+  const uint64_t n = (uint64_t)num;
+  double *d_in, *d_f; uint8_t* d_c; int32_t* d_d; uint32_t* d_nf; void* d_ws;
+  const uint64_t wsb = dcb_bytewise_workspace_bytes(n, 0);
+  BW_CK(cudaMalloc(&d_in, n * 8)); BW_CK(cudaMalloc(&d_f, n * 8)); BW_CK(cudaMalloc(&d_c, n)); BW_CK(cudaMalloc(&d_d, n * 4));
+  BW_CK(cudaMalloc(&d_nf, 4)); BW_CK(cudaMalloc(&d_ws, wsb));
+  BW_CK(cudaMemcpy(d_in, data, n * 8, cudaMemcpyHostToDevice));
+  const int rc = dcb_bytewise_compress_f64(d_in, n, 0, dc_get_abs_error_bound(), d_f, d_c, d_d, d_nf, d_ws, wsb, nullptr);
+  if (rc) die("myCompress_double", rc);
+  uint32_t nf = 0;
+  BW_CK(cudaMemcpy(&nf, d_nf, 4, cudaMemcpyDeviceToHost));
+  const uint32_t nc = (uint32_t)num - nf;
+  if (nf) {
+    double* f = (double*)realloc(*array_double, sizeof(double) * nf);
+    if (!f) { free(*array_double); printf("Error (re)allocating memory\n"); exit(1); }
+    BW_CK(cudaMemcpy(f, d_f, (size_t)nf * 8, cudaMemcpyDeviceToHost));
+    *array_double = f;
+  }
+  if (nc) {
+    char* c = (char*)realloc(*array_char, sizeof(char) * nc);
+    int* d = (int*)realloc(*array_char_displacement, sizeof(int) * nc);
+    if (!c || !d) { printf("Error (re)allocating memory\n"); exit(1); }
+    BW_CK(cudaMemcpy(c, d_c, nc, cudaMemcpyDeviceToHost));
+    BW_CK(cudaMemcpy(d, d_d, (size_t)nc * 4, cudaMemcpyDeviceToHost));
+    *array_char = c; *array_char_displacement = d;
+  }
+  cudaFree(d_in); cudaFree(d_f); cudaFree(d_c); cudaFree(d_d); cudaFree(d_nf); cudaFree(d_ws);
+  return (int)nf;
+}
+extern "C" double* myDecompress_double(double array_double[], char array_char[], int array_char_displacement[], int num) {           // :3778
+  if (dcb_device_count() == 0) die("myDecompress_double", DCB_ENODEVICE);
+  double* out = (double*)malloc(sizeof(double) * (size_t)(num > 0 ? num : 1));
+  if (num <= 0) return out;
+  uint32_t nc = 0;                                     // the reference's own walk over the displacements (see myDecompress)
+  if (array_char_displacement)
+    for (int i = 0; i < num; i++)
+      if (array_char_displacement[nc] - 1 == i) nc++;
+  const uint32_t nf = (uint32_t)num - nc;
+  const uint64_t n = (uint64_t)num;
+  double *d_f, *d_o; uint8_t* d_c; int32_t* d_d; uint32_t* d_nf;
+  BW_CK(cudaMalloc(&d_f, n * 8)); BW_CK(cudaMalloc(&d_o, n * 8)); BW_CK(cudaMalloc(&d_c, n)); BW_CK(cudaMalloc(&d_d, n * 4)); BW_CK(cudaMalloc(&d_nf, 4));
+  if (nf) BW_CK(cudaMemcpy(d_f, array_double, (size_t)nf * 8, cudaMemcpyHostToDevice));
+  if (nc) { BW_CK(cudaMemcpy(d_c, array_char, nc, cudaMemcpyHostToDevice)); BW_CK(cudaMemcpy(d_d, array_char_displacement, (size_t)nc * 4, cudaMemcpyHostToDevice)); }
+  BW_CK(cudaMemcpy(d_nf, &nf, 4, cudaMemcpyHostToDevice));
+  const int rc = dcb_bytewise_decompress_f64(d_f, d_c, d_d, d_nf, n, 0, d_o, nullptr);
+  if (rc) die("myDecompress_double", rc);
+  BW_CK(cudaMemcpy(out, d_o, n * 8, cudaMemcpyDeviceToHost));
+  cudaFree(d_f); cudaFree(d_o); cudaFree(d_c); cudaFree(d_d); cudaFree(d_nf);
+  return out;
+}

@@ -76,6 +76,8 @@ double  strtodbl(char* str);                                                    
 /* ---- CT=1: the byte-wise codec of pingpong / Himeno (impl/pingpong.c:148-161, impl/himenoBMTxps.c) ---- */
 int    myCompress(float data[], float** array_float, char** array_char, int** array_char_displacement, int num);   /* dataCompression.h:120 */
 float* myDecompress(float array_float[], char array_char[], int array_char_displacement[], int num);               /* dataCompression.h:121 */
+int     myCompress_double(double data[], double** array_double, char** array_char, int** array_char_displacement, int num);   /* impl/dataCompression.c:3815 */
+double* myDecompress_double(double array_double[], char array_char[], int array_char_displacement[], int num);             /* impl/dataCompression.c:3778 */
 
 /* ---- CT=10: Hamming SECDED over blocks of the finished stream (impl/pingpong.c:212-222, :296-311, :487-505) ----
  * BER is a compile-time macro in the reference (dataCompression.h:4); here dc_set_ber() / DC_BER, default 1e-6. */

@@ -110,6 +110,12 @@ int dcb_bytewise_compress(const float* d_in, uint64_t n, uint64_t chunk_elems, d
                           uint64_t workspace_bytes, void* cuda_stream);
 int dcb_bytewise_decompress(const float* d_float, const uint8_t* d_char, const int32_t* d_disp, const uint32_t* d_chunk_nfloat,
                             uint64_t n, uint64_t chunk_elems, float* d_out, void* cuda_stream);
+/* float64: myCompress_double (:3815) / myDecompress_double (:3778), the k-means / MM / LU callers; same layout and workspace */
+int dcb_bytewise_compress_f64(const double* d_in, uint64_t n, uint64_t chunk_elems, double abs_error_bound, double* d_double,
+                              uint8_t* d_char, int32_t* d_disp, uint32_t* d_chunk_ndouble, void* d_workspace,
+                              uint64_t workspace_bytes, void* cuda_stream);
+int dcb_bytewise_decompress_f64(const double* d_double, const uint8_t* d_char, const int32_t* d_disp,
+                                const uint32_t* d_chunk_ndouble, uint64_t n, uint64_t chunk_elems, double* d_out, void* cuda_stream);
 
 /* ---- Hamming SECDED of CT=10: hamming_encode / hamming_decode (dataCompression.c:5742, :5752), one
  * call per block of the finished stream as impl/pingpong.c:296-311 / :487-505 make them.  Block b covers bytes

@@ -79,6 +79,8 @@ int dco_hamming_decode(uint8_t* bits, char* c, int bytes, int r);         /* ret
 /* ---- byte-wise codec CT=1 (dc_oracle_bytewise.c): myCompress :3977, myDecompress :3942 ---- */
 size_t dco_bytewise_compress(const float* x, size_t n, double eb, float* af, char* ac, int* ad);   /* returns the raw-float count */
 void dco_bytewise_decompress(const float* af, const char* ac, const int* ad, size_t nc, size_t n, float* out);
+size_t dco_bytewise_compress_f64(const double* x, size_t n, double eb, double* af, char* ac, int* ad);   /* myCompress_double :3815 */
+void dco_bytewise_decompress_f64(const double* af, const char* ac, const int* ad, size_t nc, size_t n, double* out);   /* :3778 */
 
 #ifdef __cplusplus
 }

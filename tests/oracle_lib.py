@@ -581,3 +581,52 @@ def ref_bytewise_decompress(af, ac, ad, n, eb):
     lib.myDecompress.restype = _f32p
     p = lib.myDecompress(_ptr(af), _ptr(ac), _ptr(ad), int(n))
     return np.ctypeslib.as_array(p, (n,)).copy()
+
+
+def o_bytewise_compress_f64(x, eb):
+    x = _f64(x)
+    n = x.size
+    af, ac, ad = np.zeros(max(n, 1), np.float64), np.zeros(max(n, 1), np.uint8), np.zeros(max(n, 1), np.int32)
+    lib = oracle()
+    lib.dco_bytewise_compress_f64.restype = C.c_size_t
+    lib.dco_bytewise_compress_f64.argtypes = [C.c_void_p, C.c_size_t, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
+    nf = lib.dco_bytewise_compress_f64(_ptr(x), n, eb, _ptr(af), _ptr(ac), _ptr(ad))
+    return af[:nf].copy(), ac[:n - nf].copy(), ad[:n - nf].copy()
+
+
+def o_bytewise_decompress_f64(af, ac, ad, n):
+    out = np.zeros(max(n, 1), np.float64)
+    af, ac, ad = _f64(af), np.ascontiguousarray(ac, np.uint8), np.ascontiguousarray(ad, np.int32)
+    lib = oracle()
+    lib.dco_bytewise_decompress_f64.restype = None
+    lib.dco_bytewise_decompress_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p]
+    pad = lambda a: a if a.size else np.zeros(1, a.dtype)
+    lib.dco_bytewise_decompress_f64(_ptr(pad(af)), _ptr(pad(ac)), _ptr(pad(ad)), ac.size, n, _ptr(out))
+    return out[:n]
+
+
+def ref_bytewise_compress_f64(x, eb):
+    """The compiled reference's myCompress_double (impl/dataCompression.c:3815)."""
+    lib = RefLib(eb).lib
+    x = _f64(x)
+    f64p = C.POINTER(C.c_double)
+    af, ac, ad = f64p(), C.c_char_p(), C.POINTER(C.c_int)()
+    lib.myCompress_double.argtypes = [C.c_void_p, C.POINTER(f64p), C.POINTER(C.c_char_p), C.POINTER(C.POINTER(C.c_int)), C.c_int]
+    lib.myCompress_double.restype = C.c_int
+    nf = lib.myCompress_double(_ptr(x), C.byref(af), C.byref(ac), C.byref(ad), int(x.size))
+    nc = x.size - nf
+    f = np.ctypeslib.as_array(af, (nf,)).copy() if nf else np.zeros(0, np.float64)
+    c = np.frombuffer(C.string_at(ac, nc), np.uint8).copy() if nc else np.zeros(0, np.uint8)
+    d = np.ctypeslib.as_array(ad, (nc,)).copy() if nc else np.zeros(0, np.int32)
+    return f, c, d
+
+
+def ref_bytewise_decompress_f64(af, ac, ad, n, eb):
+    lib = RefLib(eb).lib
+    af = _f64(np.concatenate([af, np.zeros(1, np.float64)]))
+    ac = np.ascontiguousarray(np.concatenate([ac, np.zeros(1, np.uint8)]), np.uint8)
+    ad = np.ascontiguousarray(np.concatenate([ad, np.zeros(1, np.int32)]), np.int32)
+    lib.myDecompress_double.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    lib.myDecompress_double.restype = C.POINTER(C.c_double)
+    p = lib.myDecompress_double(_ptr(af), _ptr(ac), _ptr(ad), int(n))
+    return np.ctypeslib.as_array(p, (n,)).copy()

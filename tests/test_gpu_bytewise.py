@@ -93,3 +93,45 @@ def test_reference_symbols(dev):
         assert np.array_equal(dec.view(np.uint32), ol.o_bytewise_decompress(of, oc, od, x.size).view(np.uint32))
         assert np.max(np.abs(dec - x)) < 1.0                     # open-loop encoder: the bound drifts, not unbounded here
     L.dc_set_abs_error_bound(0.000001)
+
+
+def test_float64_device_and_symbols(dev):
+    """myCompress_double / myDecompress_double (impl/k-means.c:898-971, impl/mm.c:821, impl/lu.c:431) on the device."""
+    for name, x in inputs():
+        xd = x.astype(np.float64) * 1.000001
+        if name == "sentinel":
+            xd[[0, 3, 4100, 4101, 9000, 16383]] = -1.0
+        for chunk in (4096, 0):
+            n = xd.size
+            enc = api.bytewise_compress(torch.from_numpy(xd).to(dev), abs_error_bound=1e-4, chunk_elems=chunk)
+            out = api.bytewise_decompress(enc).cpu().numpy()
+            c_el = chunk if (chunk and chunk < n) else n
+            af, ac, ad, nf = (enc[k].cpu().numpy() for k in ("array_float", "array_char", "displacement", "nfloat"))
+            for c in range((n + c_el - 1) // c_el):
+                seg = xd[c * c_el:(c + 1) * c_el]
+                of, oc, od = ol.o_bytewise_compress_f64(seg, 1e-4)
+                b = c * c_el
+                assert int(nf[c]) == of.size
+                assert np.array_equal(af[b:b + of.size].view(np.uint64), of.view(np.uint64)), (name, chunk, c)
+                assert np.array_equal(ac[b:b + oc.size], oc) and np.array_equal(ad[b:b + od.size], od), (name, chunk, c)
+                dec = ol.o_bytewise_decompress_f64(of, oc, od, seg.size)
+                assert np.array_equal(out[b:b + seg.size].view(np.uint64), dec.view(np.uint64)), (name, chunk, c)
+    L = api.lib()
+    f64p = C.POINTER(C.c_double)
+    L.myCompress_double.argtypes = [C.c_void_p, C.POINTER(f64p), C.POINTER(C.c_char_p), C.POINTER(C.POINTER(C.c_int)), C.c_int]
+    L.myCompress_double.restype = C.c_int
+    L.myDecompress_double.argtypes = [f64p, C.c_char_p, C.POINTER(C.c_int), C.c_int]
+    L.myDecompress_double.restype = f64p
+    L.dc_set_abs_error_bound.argtypes = [C.c_double]
+    L.dc_set_abs_error_bound(0.001)
+    x = np.cumsum(np.random.default_rng(2).normal(0, 1e-3, 6000)) + 2.0
+    af, ac, ad = f64p(), C.c_char_p(), C.POINTER(C.c_int)()
+    nf = L.myCompress_double(x.ctypes.data, C.byref(af), C.byref(ac), C.byref(ad), x.size)
+    of, oc, od = ol.o_bytewise_compress_f64(x, 0.001)
+    assert nf == of.size and np.array_equal(np.ctypeslib.as_array(af, (nf,)).view(np.uint64), of.view(np.uint64))
+    nc = x.size - nf
+    assert C.string_at(ac, nc) == oc.tobytes() and np.array_equal(np.ctypeslib.as_array(ad, (nc,)), od)
+    p = L.myDecompress_double(af, ac, ad, x.size)
+    dec = np.ctypeslib.as_array(p, (x.size,))
+    assert np.array_equal(dec.view(np.uint64), ol.o_bytewise_decompress_f64(of, oc, od, x.size).view(np.uint64))
+    L.dc_set_abs_error_bound(0.000001)

@@ -46,3 +46,20 @@ def test_layout_invariants():
     f, c, d = ol.o_bytewise_compress(x, 0.01)
     assert f.size + c.size == x.size and np.all(np.diff(d) > 0) and d.min() >= 5 and d.max() <= x.size
     assert set(np.unique(c)) <= set(b"abcd")
+
+
+@pytest.mark.parametrize("eb", (0.01, 1e-4))
+def test_float64_matches_reference(eb):
+    if not ol.build_ref(eb):
+        pytest.skip("oracle/_ref not built (no /root/reference here)")
+    for name, x in fields():
+        xd = x.astype(np.float64) * 1.000001
+        if name == "sentinel":
+            xd[[0, 2, 50, 51, 52, 53, 900, 2999]] = -1.0
+        of, oc, od = ol.o_bytewise_compress_f64(xd, eb)
+        rf, rc, rd = ol.ref_bytewise_compress_f64(xd, eb)
+        assert np.array_equal(of.view(np.uint64), rf.view(np.uint64)), (name, eb)
+        assert np.array_equal(oc, rc) and np.array_equal(od, rd), (name, eb)
+        dec = ol.o_bytewise_decompress_f64(of, oc, od, xd.size)
+        ref = ol.ref_bytewise_decompress_f64(rf, rc, rd, xd.size, eb)
+        assert np.array_equal(dec.view(np.uint64), ref.view(np.uint64)), (name, eb)
