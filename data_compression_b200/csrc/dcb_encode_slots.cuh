@@ -12,7 +12,7 @@
 // known; tile offsets therefore retire IN ORDER, and the r1 profiles show what that costs -- a ticket, a status word, a
 // scanner block, a copy-out deferred by two iterations behind five barriers, and every slow tile (CT=7's exact walk)
 // stalls the blocks behind it (mean iteration 7.2 us against 5.6 us of work).  Here a block never waits for another one:
-// two barriers per tile (statistics, scan), static tile assignment, the packed tile leaves as aligned 128-bit stores
+// two barriers per tile (statistics, scan), tiles from a ticket counter (pure load balancing), the packed tile leaves as aligned 128-bit stores
 // without a funnel shift.  The price is pass 2: the compressed bytes are written and read once more (2B of extra traffic,
 // B = 4n/r; 0.2 GB for the smooth field, most of it L2 hits), which is far less than what the coupling cost.
 #pragma once
