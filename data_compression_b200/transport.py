@@ -152,17 +152,24 @@ def recv_compressed(n, chunk_elems, src, device, compressed_cls, group=None, str
 
 
 def pingpong_hop_crc(comp, peer, is_sender, n, chunk_elems, device, compressed_cls,
-                     crc_fn: Callable, corrupt_fn: Optional[Callable] = None, max_resend=8, group=None):
+                     crc_fn: Callable, corrupt_fn: Optional[Callable] = None, max_resend=8, group=None, hamming=None):
     """CT=8/9 hop.  Sender (impl/pingpong.c:260-289): send stream + per-chunk CRC (they travel in the table), wait for
     the one-byte ack, resend on 'n'.  Receiver (:363-447): [test hook: corrupt the received stream, the reference's
-    bit_flip], recompute the CRC of what arrived, compare, ack.  Returns (Compressed the receiver holds | None, resends)."""
+    bit_flip], recompute the CRC of what arrived, compare, ack.  Returns (Compressed the receiver holds | None, resends).
+    CT=10 (impl/pingpong.c:290-326, :448-510): hamming = (block_bytes, encode_fn, decode_fn).  The sender also sends the SECDED
+    check words of every block of the stream (encode_fn(stream, total, block_bytes) -> int32[blocks]); the receiver runs
+    decode_fn(stream, total, block_bytes, check) on what arrived -- single-bit errors are rectified in place -- BEFORE the CRC
+    comparison, so a one-bit fault per block costs no resend."""
     import torch
     import torch.distributed as dist
     resend = 0
     ack = torch.zeros(1, dtype=torch.uint8, device=device)
     while True:
         if is_sender:
-            send_compressed(comp, peer, group=group)
+            f = send_compressed(comp, peer, group=group)
+            if hamming is not None and f.stream.numel():
+                chk = hamming[1](f.stream, f.stream.numel(), hamming[0])
+                dist.send(chk.contiguous(), peer, group=group)
             dist.recv(ack, peer, group=group)
             if ack.item() == ord("y") or resend >= max_resend:
                 return None, resend
@@ -172,6 +179,12 @@ def pingpong_hop_crc(comp, peer, is_sender, n, chunk_elems, device, compressed_c
             if corrupt_fn is not None:
                 corrupt_fn(got, resend)
             K = got.chunk_offsets.numel() - 1
+            total = int(got.chunk_offsets[-1].item()) if K else 0
+            if hamming is not None and total:
+                nb = (total + hamming[0] - 1) // hamming[0]
+                chk = torch.zeros(nb, dtype=torch.int32, device=device)
+                dist.recv(chk, peer, group=group)
+                hamming[2](got.stream, total, hamming[0], chk)
             ok = bool((crc_fn(got.stream, got.chunk_offsets)[:K] == got.chunk_crc[:K]).all().item())
             ack[0] = ord("y") if ok else ord("n")
             dist.send(ack, peer, group=group)

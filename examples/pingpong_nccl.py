@@ -39,8 +39,14 @@ def main():
     assert dist.get_world_size() == 2
     peer = 1 - rank
     x = make_field(a.field, a.n)
-    crc = a.ct in (8, 9)
-    comp = api.compress(torch.from_numpy(x).to(dev), ct=a.ct, abs_error_bound=a.eb, chunk_elems=a.chunk) if rank == 0 else None
+    crc = a.ct in (8, 9, 10)
+    cct = 8 if a.ct == 10 else a.ct                              # CT=10 = the CT=5 stream + CRC + Hamming SECDED blocks (impl/pingpong.c:290-326)
+    comp = api.compress(torch.from_numpy(x).to(dev), ct=cct, abs_error_bound=a.eb, chunk_elems=a.chunk) if rank == 0 else None
+    hamming = None
+    if a.ct == 10:
+        def hm_dec(stream, total, bs, chk):
+            api.hamming_decode(stream, total, bs, chk)
+        hamming = (125000, lambda s_, t_, b_: api.hamming_encode(s_, t_, b_)[0], hm_dec)     # block_size at BER = 1e-6 (:5868)
     resends = 0
     flipped = [False]
 
@@ -56,7 +62,7 @@ def main():
         sender = (hop % 2) == rank
         if crc:
             got, r = tr.pingpong_hop_crc(comp, peer, sender, a.n, a.chunk, dev, api.Compressed, api.crc32_chunks,
-                                         corrupt_fn=corrupt if (hop == 0 and not sender) else None)
+                                         corrupt_fn=corrupt if (hop == 0 and not sender) else None, hamming=hamming)
             resends += r
         elif sender:
             tr.send_compressed(comp, peer)
@@ -77,7 +83,7 @@ def main():
         if a.check:
             sys.path.insert(0, os.path.join(ROOT, "tests"))
             import oracle_lib as ol
-            base = 5 if a.ct in (5, 8) else (7 if a.ct in (7, 9) else a.ct)
+            base = 5 if a.ct in (5, 8, 10) else (7 if a.ct in (7, 9) else a.ct)
             enc = ol.o_compress_chunked(base, x, a.chunk, a.eb)
             want = ol.o_decompress_chunked(base, enc, a.n, a.chunk, a.eb)
             same = np.array_equal(out.view(np.uint32), want.view(np.uint32)) and \

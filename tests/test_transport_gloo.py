@@ -43,6 +43,10 @@ def oracle_compressed(x, ct, chunk, eb):
                           torch.from_numpy(enc["chunk_crc"].view(np.int32).copy())), enc
 
 
+def _pack_check(c):
+    return sum((1 << i) for i, ch in enumerate(c) if ch == ord("1"))
+
+
 def crc_chunks(stream, offsets):
     s, o = stream.numpy(), offsets.numpy()
     return torch.from_numpy(np.array([ol.o_crc32(s[o[c]:o[c + 1]]) for c in range(o.size - 1)], dtype=np.uint32).view(np.int32))
@@ -122,6 +126,25 @@ def _worker(rank, world, port, q):
         assert resends == 1
         if rank == 1:
             x0 = make_field("smooth", n, start=0)
+            assert np.array_equal(got.stream[:int(got.chunk_offsets[-1])].numpy(), oracle_compressed(x0, 8, chunk, eb)[1]["stream"])
+        # ---- CT=10 hop (impl/pingpong.c:290-326, :448-510): the same single-bit fault is rectified by the Hamming blocks ----
+        def hm_encode(stream, total, bs):
+            sn = stream.numpy()
+            return torch.tensor([_pack_check(ol.o_hamming_encode(sn[b:min(total, b + bs)])[1]) for b in range(0, total, bs)], dtype=torch.int32)
+
+        def hm_decode(stream, total, bs, chk):
+            sn = stream.numpy()
+            for i, b in enumerate(range(0, total, bs)):
+                blk = sn[b:min(total, b + bs)]
+                r = ol.o_hm_length(8 * blk.size)
+                c = bytes(ord("0") + ((int(chk[i]) >> k) & 1) for k in range(r + 1))
+                _, fixed, _ = ol.o_hamming_decode(blk, c, r)
+                sn[b:b + blk.size] = fixed
+
+        got, resends = tr.pingpong_hop_crc(comp, peer, rank == 0, n, chunk, dev, HostCompressed, crc_chunks,
+                                           corrupt_fn=corrupt if rank == 1 else None, hamming=(512, hm_encode, hm_decode))
+        assert resends == 0
+        if rank == 1:
             assert np.array_equal(got.stream[:int(got.chunk_offsets[-1])].numpy(), oracle_compressed(x0, 8, chunk, eb)[1]["stream"])
         q.put((rank, "ok"))
     except Exception as e:  # pragma: no cover
