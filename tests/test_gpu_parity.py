@@ -335,3 +335,28 @@ def test_every_encoder_kernel(encoder):
     r = subprocess.run([sys.executable, "-m", "pytest", here, "-x", "-q", "-m", "gpu", "-k", sel, "-p", "no:cacheprovider"],
                        env=env, capture_output=True, text=True, cwd=os.path.dirname(os.path.dirname(here)))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_ct7_mask_decision_at_scale(dev):
+    """The CT=7 mask comes from a BOUND on the reference's sequential float32 sum whenever the bound pins its 17 bits (DESIGN.md
+    4.3), from the exact transducer sum otherwise.  4 x 1024 chunks of differently distributed data: every chunk's mask and type
+    must equal med_dataset_float's (computed by the oracle on the min-subtracted chunk), under the default encoder."""
+    rng = np.random.default_rng(77)
+    n, chunk = 1 << 22, 4096
+    fields = {
+        "lognormal": rng.lognormal(0.0, 2.0, n),
+        "offset": 1000.0 + rng.uniform(0, 1e-2, n),                 # large minimum, tiny spread: cancellation in the raw sums
+        "tiny": rng.uniform(0, 1e-30, n),
+        "steps": np.repeat(rng.uniform(0, 100, n // 512), 512) + rng.normal(0, 1e-3, n),
+    }
+    for name, xf in fields.items():
+        x = xf.astype(np.float32)
+        comp = api.compress(torch.from_numpy(x).to(dev), ct=7, abs_error_bound=1e-3, chunk_elems=chunk)
+        torch.cuda.synchronize()
+        med = comp.chunk_medium[:n // chunk].cpu().numpy().view(np.uint32) >> 15
+        typ = comp.chunk_type[:n // chunk].cpu().numpy()
+        for c in range(n // chunk):
+            seg = x[c * chunk:(c + 1) * chunk]
+            _, y = ol.o_min_subtract(seg)
+            m, t = ol.o_med(y, 0)
+            assert int(med[c]) == ol.mask17_of(m) and int(typ[c]) == t, (name, c, hex(int(med[c])), hex(ol.mask17_of(m)))
