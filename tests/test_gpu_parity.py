@@ -360,3 +360,36 @@ def test_ct7_mask_decision_at_scale(dev):
             _, y = ol.o_min_subtract(seg)
             m, t = ol.o_med(y, 0)
             assert int(med[c]) == ol.mask17_of(m) and int(typ[c]) == t, (name, c, hex(int(med[c])), hex(ol.mask17_of(m)))
+
+
+@pytest.mark.parametrize("seed", (1, 2, 3))
+def test_fuzz_mixed_fields(seed, dev):
+    """Seeded mixtures of everything a chunk can hold -- smooth, noisy, constant, ramps, zeros, denormals, values near the
+    error bound, lognormal magnitudes -- at ragged sizes, every CT, random error bounds: stream, tables, CRCs and decoded floats
+    against the oracle (min-subtract on: values stay in the format's domain)."""
+    rng = np.random.default_rng(1000 + seed)
+    pieces = []
+    for _ in range(40):
+        m = int(rng.integers(100, 9000))
+        kind = int(rng.integers(0, 8))
+        if kind == 0:
+            p = make_field("smooth", m, start=int(rng.integers(0, 60000)))
+        elif kind == 1:
+            p = make_field("noisy", m, start=int(rng.integers(0, 1 << 20)))
+        elif kind == 2:
+            p = np.full(m, rng.uniform(0, 50), np.float32)
+        elif kind == 3:
+            p = (np.arange(m) * rng.uniform(1e-4, 1e-1) + rng.uniform(0, 10)).astype(np.float32)
+        elif kind == 4:
+            p = np.zeros(m, np.float32)
+        elif kind == 5:
+            p = (rng.random(m) * 1e-39).astype(np.float32)
+        elif kind == 6:
+            p = (rng.uniform(0, 3, m) * rng.choice([1e-3, 1e-2, 1e-1])).astype(np.float32)
+        else:
+            p = (rng.lognormal(0, 3, m)).astype(np.float32)
+        pieces.append(p.astype(np.float32))
+    x = np.concatenate(pieces)
+    for ct in CTS:
+        eb = float(rng.choice(EBS))
+        assert_same_as_oracle(x, ct, eb, 4096, dev, tag="fuzz seed=%d ct=%d eb=%g n=%d" % (seed, ct, eb, x.size))
