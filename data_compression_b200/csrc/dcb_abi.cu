@@ -848,6 +848,11 @@ extern "C" int dcb_hamming_decode(uint8_t* d_bits, uint64_t total_bytes, uint32_
 }
 
 #ifdef DCB_DEBUG_MED
+extern "C" int dcb_debug_exact(unsigned long long* host_dst) {
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpyFromSymbol(host_dst, g_dbg_exact, sizeof(g_dbg_exact)));
+  return DCB_OK;
+}
 extern "C" int dcb_debug_walk(unsigned long long* host_dst) {
   CK(cudaDeviceSynchronize());
   CK(cudaMemcpyFromSymbol(host_dst, g_dbg_walk, sizeof(g_dbg_walk)));

@@ -28,6 +28,9 @@
 #define DCB_WR 512                  // elements per round (32 lanes x 16)
 #define DCB_WWORDS 520              // words of the round buffer: 512 codes of <= 32 bits + carry word + slack
 
+#ifdef DCB_DEBUG_MED
+__device__ unsigned long long g_dbg_exact[4];   // cycles in exact_medium, calls, cycles per whole chunk, chunks
+#endif
 struct WarpBuf {
   float X[2][32 * DCB_XPITCH];      // classification pass: double-buffered rounds, one 80-byte slot per lane
   float4 P[128];                    // statistics pass of the next chunk: one round, linear
@@ -349,7 +352,13 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
       }
       if (!decided) {
         float total, ymx, y0;
+#ifdef DCB_DEBUG_MED
+        const long long dbg_t0 = clock64();
+#endif
         exact_medium(a, sm, cbase, cend, mn, submin, slow, cbulk, lane, total, ymx, y0);
+#ifdef DCB_DEBUG_MED
+        if (lane == 0) { atomicAdd(&g_dbg_exact[0], (unsigned long long)(clock64() - dbg_t0)); atomicAdd(&g_dbg_exact[1], 1ull); }
+#endif
         const float med = __fdiv_rn(total, fc);
         type = slow ? ((y0 != y0) ? 0 : type_from_max(ymx)) : type_from_max(submin ? __fsub_rn(lmx, mn) : lmx);
         mask17 = f2u(med) >> 15;
