@@ -112,26 +112,24 @@ extern "C" uint64_t dcb_workspace_bytes(uint64_t n, uint64_t chunk) {
   return ws_head_bytes(n);
 }
 
-static int g_num_sms = 0;
-static int num_sms() {
-  if (g_num_sms == 0) {
-    int dev = 0, n = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
-      g_num_sms = n;
-    else
-      g_num_sms = 148;
+static int num_sms() {                                 // per device (a process may drive several GPUs)
+  static std::atomic<int> cache[64];
+  int dev = 0, n = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  n = cache[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev].store(n, std::memory_order_relaxed);
   }
-  return g_num_sms;
+  return n;
 }
 
 // persistent launch: DCB_ENC_BLOCKS_PER_SM resident blocks per SM pull tiles from the ticket counter
 template <int CT>
 static cudaError_t launch_encode(const EncArgs& a, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  {                                                   // per device; cheap enough to set on every launch
     cudaError_t e = cudaFuncSetAttribute(dcb_encode_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   // one block becomes the prefix scanner, the others are workers
   const unsigned grid = 1u + (unsigned)min((uint64_t)a.num_tiles, (uint64_t)num_sms() * DCB_ENC_BLOCKS_PER_SM - 1u);
@@ -159,12 +157,10 @@ extern "C" int dcb_profile_last_ms(float* encode_ms, float* compact_ms) {
 
 template <int CT>
 static cudaError_t launch_encode_warp(const EncArgs& a, const CompactArgs& ca, cudaStream_t st) {
-  static bool attr_set = false;
   const int smem = (int)(sizeof(WarpBuf) * (DCB_WNT / 32));
-  if (!attr_set) {
+  {
     cudaError_t e = cudaFuncSetAttribute(dcb_encode_warp_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   const uint64_t blocks = ((uint64_t)a.num_tiles + DCB_WNT / 32 - 1) / (DCB_WNT / 32);
   const unsigned grid = (unsigned)min(blocks, (uint64_t)num_sms() * (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 : DCB_WARP_BLOCKS));
@@ -180,11 +176,9 @@ static cudaError_t launch_encode_warp(const EncArgs& a, const CompactArgs& ca, c
 
 template <int CT>
 static cudaError_t launch_encode_slots(const EncArgs& a, const CompactArgs& ca, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  {                                                   // per device; cheap enough to set on every launch
     cudaError_t e = cudaFuncSetAttribute(dcb_encode_slots_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SlotSmem));
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   const unsigned grid = (unsigned)min((uint64_t)a.num_tiles, (uint64_t)num_sms() * DCB_SLOT_BLOCKS_PER_SM);
   PROF_MARK(0);
@@ -334,7 +328,10 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
 
 template <int CT>
 static cudaError_t launch_decode(const DecArgs& a, cudaStream_t st) {
-  dcb_decode_kernel<CT><<<(unsigned)((a.num_chunks + DEC_NT - 1) / DEC_NT), DEC_NT, 0, st>>>(a);
+  // (the attribute is per device, and setting it is cheap: no process-wide "already set" flag)
+  cudaError_t e = cudaFuncSetAttribute(dcb_decode_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DEC_SMEM_BYTES);
+  if (e != cudaSuccess) return e;
+  dcb_decode_kernel<CT><<<(unsigned)((a.num_chunks + DEC_NT - 1) / DEC_NT), DEC_NT, DEC_SMEM_BYTES, st>>>(a);
   return cudaGetLastError();
 }
 

@@ -25,8 +25,16 @@
 #endif
 #define DEC_NT 128
 #define DEC_RND 8
-#define DEC_RING_WORDS 32          // 8 copies of 16 B per lane
-#define DEC_PITCH 36               // ring pitch in words (144 B: 16-byte aligned, lanes start in different banks)
+#ifndef DEC_RING_BLOCKS
+#define DEC_RING_BLOCKS 8          // 16-byte copies per lane ring (power of two)
+#endif
+#ifndef DEC_WAIT_GROUPS
+#define DEC_WAIT_GROUPS 2          // cp.async groups (one per round) that may still be in flight when a round starts: a block
+#endif                             // issued R rounds ago is needed no sooner than (DEC_RING_BLOCKS - 1) / 2 rounds later
+#define DEC_RING_WORDS (4 * DEC_RING_BLOCKS)
+#define DEC_PITCH (DEC_RING_WORDS + 4)   // ring pitch in words (16-byte aligned, lanes start in different banks)
+#define DEC_STR2(x) #x
+#define DEC_STR(x) DEC_STR2(x)
 
 __device__ __forceinline__ void dec_cp_async16(uint32_t smem_dst, const void* gsrc) {
   // .cg: the stream is read once and every lane walks its own lines -- allocating them in L1 (.ca) made the L1 miss
@@ -56,19 +64,19 @@ struct LaneReader {
   const uint8_t* gbase;   // address of block 0
 
   __device__ __forceinline__ void fetch_if(bool want) {
-    if (want && fetched < nblocks) dec_cp_async16(ring + ((fetched & 7u) << 4), gbase + ((size_t)fetched << 4));
+    if (want && fetched < nblocks) dec_cp_async16(ring + ((fetched & (DEC_RING_BLOCKS - 1u)) << 4), gbase + ((size_t)fetched << 4));
     fetched += want ? 1u : 0u;
   }
   // Called once per round (<= 8 codes, <= 32 bytes consumed since the last call): keep 7 blocks ahead of the current one
   // in flight; a block is recycled only after the position has left it.  One commit per call, so "all but the two
   // newest groups" always covers every block the coming round can touch.
   __device__ __forceinline__ void top_up() {
-    const uint32_t want_until = ((pos - 64u) >> 7) + 8u;             // blocks cur .. cur+7
+    const uint32_t want_until = ((pos - 64u) >> 7) + DEC_RING_BLOCKS;   // blocks cur .. cur + DEC_RING_BLOCKS - 1
     fetch_if(fetched < want_until);
     fetch_if(fetched < want_until);
     fetch_if(fetched < want_until);
     dec_cp_commit();
-    asm volatile("cp.async.wait_group 2;\n" ::: "memory");
+    asm volatile("cp.async.wait_group " DEC_STR(DEC_WAIT_GROUPS) ";\n" ::: "memory");
   }
   __device__ __forceinline__ uint32_t ring_word(uint32_t word) const {
     return lds32(ring + ((word & (DEC_RING_WORDS - 1u)) << 2));
@@ -90,7 +98,7 @@ struct LaneReader {
     const uint32_t bitpos = (uint32_t)(byte_off & 15ull) * 8u;
     pos = bitpos + 64u;
     #pragma unroll
-    for (int b = 0; b < 8; b++) fetch_if(true);
+    for (int b = 0; b < DEC_RING_BLOCKS; b++) fetch_if(true);
     dec_cp_commit();
     asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     const uint32_t wi = bitpos >> 5;
@@ -238,11 +246,13 @@ __device__ __forceinline__ void decode_round(LaneReader& br, const CodecConst& k
 
 #define DEC_SUPER 32                // codes per lane between two coalesced write-outs
 #define DEC_OPITCH 36               // floats per lane row of the output staging (144 B: conflict-free 128-bit accesses)
+#define DEC_SMEM_BYTES (DEC_NT * (DEC_PITCH + DEC_OPITCH) * 4)
 
 template <int CT>
-__global__ void __launch_bounds__(DEC_NT, 6) dcb_decode_kernel(const DecArgs a) {
-  __shared__ __align__(16) uint32_t rings[DEC_NT * DEC_PITCH];
-  __shared__ __align__(16) float ostage[DEC_NT * DEC_OPITCH];
+__global__ void __launch_bounds__(DEC_NT, (DEC_RING_BLOCKS > 8 ? 4 : 6)) dcb_decode_kernel(const DecArgs a) {
+  extern __shared__ __align__(16) unsigned char dec_smem[];          // DEC_SMEM_BYTES: per-lane stream rings, then the output staging
+  uint32_t* const rings = reinterpret_cast<uint32_t*>(dec_smem);
+  float* const ostage = reinterpret_cast<float*>(dec_smem + DEC_NT * DEC_PITCH * 4);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint64_t c_raw = (uint64_t)blockIdx.x * DEC_NT + threadIdx.x;
   const bool active = c_raw < a.num_chunks;

@@ -75,8 +75,7 @@ __device__ __forceinline__ void classify_pred(uint32_t& fields, uint32_t& miss, 
       "min.f32 dm, a1, a2;\n\t"
       "min.f32 dm, dm, a3;\n\t"
       "setp.gt.f32 pnz, %2, %6;\n\t"
-      "setp.le.and.f32 ph, dm, %7, pnz;\n\t"
-      "setp.gt.and.f32 pm, dm, %7, pnz;\n\t"
+      "setp.le.and.f32 ph|pm, dm, %7, pnz;\n\t"      /* pm = !(dm <= tp) && pnz: one FSETP, two predicates */
       "setp.neu.and.f32 pa, a1, dm, ph;\n\t"
       "setp.neu.and.f32 pb, a2, dm, pa;\n\t"
       "@ph mad.lo.u32 %0, %8, %9, %0;\n\t"

@@ -31,6 +31,17 @@
 #ifdef DCB_DEBUG_MED
 __device__ unsigned long long g_dbg_exact[4];   // cycles in exact_medium, calls, cycles per whole chunk, chunks
 #endif
+#ifndef DCB_PACKED
+#define DCB_PACKED 1                // classification arithmetic on sm_100 packed fp32 pairs (FADD2): two elements per instruction
+#endif
+// Packed fp32 (PTX add/sub/mul.rn.f32x2, sm_100+; SASS FADD2 / FMUL2): every half is an IEEE round-to-nearest operation of
+// its own, so the reference's per-operation float32 rounding (dataCompression.c:3362-3364) is kept bit for bit
+// (tools/probe_f32x2.cu checks that on the device against __fadd_rn / __fmul_rn: 2^28 quadruples, 0 mismatches).
+__device__ __forceinline__ uint64_t pk2(float lo, float hi) { uint64_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk2(uint64_t r, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(r)); }
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) { uint64_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ uint64_t sub2(uint64_t a, uint64_t b) { uint64_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+
 struct WarpBuf {
   float X[2][32 * DCB_XPITCH];      // classification pass: double-buffered rounds, one 80-byte slot per lane
   float4 P[128];                    // statistics pass of the next chunk: one round, linear
@@ -208,6 +219,17 @@ __device__ __noinline__ void exact_medium(const EncArgs& a, WarpBuf& sm, uint64_
     // lanes that straddle a binade (their 16 values one by one): one or two stops in most rounds.
     const bool certain = d0 >= 0.0f;
     const unsigned cm = __ballot_sync(0xffffffffu, certain);
+    // The common round: every lane is a transducer of the SAME binade and none depends on the parity of S (no tie in its 16
+    // additions).  Then S_out = S_in + sum of the d0, and that sum is exact in any order (multiples of the binade's grid below
+    // 2^24 grid steps): one butterfly instead of the segmented scan and the walk.
+    const uint32_t ebits0 = __shfl_sync(0xffffffffu, ebits, 0);
+    if (cm == 0xffffffffu && __all_sync(0xffffffffu, d0 == d1 && ebits == ebits0)) {
+      float t = d0;
+      #pragma unroll
+      for (int o = 16; o; o >>= 1) t = __fadd_rn(t, __shfl_xor_sync(0xffffffffu, t, o));
+      S = __fadd_rn(S, t);
+      continue;
+    }
     const uint32_t eprev = __shfl_up_sync(0xffffffffu, ebits, 1);
     const bool head = certain && (lane == 0 || !((cm >> (lane - 1)) & 1u) || eprev != ebits);
     const unsigned hm = __ballot_sync(0xffffffffu, head);
@@ -404,6 +426,26 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
         const float4 v = *reinterpret_cast<const float4*>(slot + 4 * q);
         x[4 * q] = v.x; x[4 * q + 1] = v.y; x[4 * q + 2] = v.z; x[4 * q + 3] = v.w;
       }
+#if DCB_PACKED
+      // element e and element e + 8 as the two halves of one 64-bit register: the min-subtract writes the pair (a scalar FADD per
+      // half, inside one asm block so that ptxas allocates the two results as the pair instead of moving them there)
+      uint64_t XP[DCB_E / 2];
+      if (cbase + (uint64_t)(j + 1) * DCB_WR > cend) {     // warp-uniform: a ragged round, padding becomes 0.0f
+        #pragma unroll
+        for (int e = 0; e < DCB_E; e++) x[e] = (e < vcnt) ? x[e] : mn;
+      }
+      if (slow && !submin) {                               // rare: NaN payloads must survive, so no arithmetic at all
+        #pragma unroll
+        for (int e = 0; e < DCB_E / 2; e++) XP[e] = pk2(x[e], x[e + 8]);
+      } else {
+        #pragma unroll
+        for (int e = 0; e < DCB_E / 2; e++)
+          asm("{\n\t.reg .f32 lo, hi;\n\tsub.rn.f32 lo, %1, %3;\n\tsub.rn.f32 hi, %2, %3;\n\tmov.b64 %0, {lo, hi};\n\t}"
+              : "=l"(XP[e]) : "f"(x[e]), "f"(x[e + 8]), "f"(mn));              // mn = 0.0f without min-subtract: x - 0 is x
+      }
+      #pragma unroll
+      for (int e = 0; e < DCB_E / 2; e++) upk2(XP[e], x[e], x[e + 8]);
+#else
       if (submin) {
         if (cbase + (uint64_t)(j + 1) * DCB_WR <= cend) {   // warp-uniform: a full round
           #pragma unroll
@@ -413,6 +455,7 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
           for (int e = 0; e < DCB_E; e++) x[e] = (e < vcnt) ? __fsub_rn(x[e], mn) : 0.0f;
         }
       }
+#endif
       float h1 = __shfl_up_sync(0xffffffffu, x[DCB_E - 1], 1);
       float h2 = __shfl_up_sync(0xffffffffu, x[DCB_E - 2], 1);
       float h3 = __shfl_up_sync(0xffffffffu, x[DCB_E - 3], 1);
@@ -425,13 +468,38 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
       uint32_t total = 0;
       bool all3 = false;
       int np = DCB_E;                                  // pieces the packing loop has to place (warp-uniform)
+      bool uni48 = false;                              // warp-uniform: every lane holds sixteen 3-bit codes (48 bits)
       if (!slow) {
         uint32_t miss = 0u;                              // bit e: element e needs a fallback code
         if (CT != CT_NP) {
-          float b1 = h1, b2 = h2, b3 = h3;
-          float t1 = __fmul_rn(3.0f, b1), t2 = __fmul_rn(3.0f, b2);
           uint32_t fa = 0x92492490u, fb = 0x92490000u;   // 3-bit fields of elements 0..9 / 10..15, all preset to 100 (zero)
           const float tp3 = first ? -1.0f : a.k.tp;      // chunk start: elements 0..2 never hit
+#if DCB_PACKED
+          // The encoder is open loop (history = the INPUT values, :3386-3388), so elements are independent: element e and
+          // element e + 8 of this lane share every instruction of the predictor arithmetic as the two halves of a packed
+          // pair.  3*b is fl(2b + b): 2b is exact, so the sum rounds once, exactly like the reference's 3*b (and ptxas cannot
+          // contract two additions into an FFMA2, which it does with mul.rn.f32x2 followed by sub.rn.f32x2).
+          uint64_t B1 = pk2(h1, x[7]), B2 = pk2(h2, x[6]), B3 = pk2(h3, x[5]);
+          uint64_t W1 = add2(B1, B1), W2 = add2(B2, B2);                      // 2*b1, 2*b2
+          uint64_t T1 = add2(W1, B1), T2 = add2(W2, B2);                      // 3*b1, 3*b2
+          #define DCB_CLS2(E, ACCL, POSL, TPL, ACCH, POSH) do {                                                    \
+              const uint64_t X = XP[E];                                                                            \
+              const uint64_t D1 = sub2(B1, X);                                                                     \
+              const uint64_t D2 = sub2(sub2(W1, B2), X);                                                           \
+              const uint64_t D3 = sub2(add2(sub2(T1, T2), B3), X);                                                 \
+              float d1l, d1h, d2l, d2h, d3l, d3h;                                                                  \
+              upk2(D1, d1l, d1h); upk2(D2, d2l, d2h); upk2(D3, d3l, d3h);                                          \
+              classify_pred<(1u << (POSL))>(ACCL, miss, x[E], d1l, d2l, d3l, a.k.tz, TPL, one, 1u << (E));         \
+              classify_pred<(1u << (POSH))>(ACCH, miss, x[(E) + 8], d1h, d2h, d3h, a.k.tz, a.k.tp, one, 1u << ((E) + 8)); \
+              B3 = B2; B2 = B1; B1 = X; T2 = T1; W1 = add2(X, X); T1 = add2(W1, X);                                \
+            } while (0)
+          DCB_CLS2(0, fa, 29, tp3, fa, 5); DCB_CLS2(1, fa, 26, tp3, fa, 2); DCB_CLS2(2, fa, 23, tp3, fb, 29);
+          DCB_CLS2(3, fa, 20, a.k.tp, fb, 26); DCB_CLS2(4, fa, 17, a.k.tp, fb, 23); DCB_CLS2(5, fa, 14, a.k.tp, fb, 20);
+          DCB_CLS2(6, fa, 11, a.k.tp, fb, 17); DCB_CLS2(7, fa, 8, a.k.tp, fb, 14);
+          #undef DCB_CLS2
+#else
+          float b1 = h1, b2 = h2, b3 = h3;
+          float t1 = __fmul_rn(3.0f, b1), t2 = __fmul_rn(3.0f, b2);
           #define DCB_CLS(E, ACC, POS, TP) do {                                                                   \
               const float xe = x[E];                                                                               \
               const float p2 = __fsub_rn(__fadd_rn(b1, b1), b2);             /* 2*b1 is exact */                   \
@@ -446,6 +514,7 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
           DCB_CLS(10, fb, 29, a.k.tp); DCB_CLS(11, fb, 26, a.k.tp); DCB_CLS(12, fb, 23, a.k.tp); DCB_CLS(13, fb, 20, a.k.tp);
           DCB_CLS(14, fb, 17, a.k.tp); DCB_CLS(15, fb, 14, a.k.tp);
           #undef DCB_CLS
+#endif
           chi = fa | (fb >> 30); clo = fb << 2;          // the 48-bit string: 30 bits of fa, 18 bits of fb
           all3 = (vcnt == DCB_E) && (miss == 0u);
         }
@@ -455,6 +524,7 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
         const bool warp_all3 = __all_sync(0xffffffffu, all3);
         const bool head_ok = all3 || (CT != CT_NP && first && vcnt == DCB_E && (miss & ~7u) == 0u);
         const bool headcase = !warp_all3 && __all_sync(0xffffffffu, head_ok);
+        uni48 = warp_all3;
         if (warp_all3) {
           total = 48u;
         } else if (headcase) {
@@ -528,16 +598,24 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
       c3 = __shfl_sync(0xffffffffu, x[DCB_E - 3], 31);
 
       // ---- warp scan of the bit counts; the round starts at bit carry_bits of the buffer -----------------------------
-      uint32_t incl = total;
-      #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += t;
+      uint32_t incl, R;
+      unsigned havebits = 0xffffffffu;
+      bool fast_pack = true;
+      if (uni48) {                                                              // the common round of compressible data: no scan
+        incl = 48u * (uint32_t)(lane + 1);
+        R = carry_bits + 32u * 48u;
+      } else {
+        incl = total;
+        #pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += t;
+        }
+        R = carry_bits + __shfl_sync(0xffffffffu, incl, 31);                    // bits in the buffer after this round
+        havebits = __ballot_sync(0xffffffffu, total > 0u);
+        fast_pack = __all_sync(0xffffffffu, total >= 32u || total == 0u);
       }
-      const uint32_t R = carry_bits + __shfl_sync(0xffffffffu, incl, 31);       // bits in the buffer after this round
       const uint32_t s = carry_bits + incl - total;                             // first bit of this lane
-      const unsigned havebits = __ballot_sync(0xffffffffu, total > 0u);
-      const bool fast_pack = __all_sync(0xffffffffu, total >= 32u || total == 0u);
 
       // ---- pack ----------------------------------------------------------------------------------------------------
       uint32_t hi = 0u;
