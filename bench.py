@@ -57,6 +57,9 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-threads", type=int, default=2, help="host threads making the blocking host-pointer calls")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--sweep", default="full", choices=("full", "quick", "none"),
+                    help="extra workloads measured after the headline and reported under \"sweep\" (BASELINE.json configs 1, 3, 5)")
+    ap.add_argument("--sweep-steps", type=int, default=5)
     ap.add_argument("--cpu-log2n", type=int, default=28, help="bounded CPU sample = 2^cpu_log2n elements (default: the whole per-GPU field, ~15 s of CPU work over 16 cores)")
     return ap.parse_args()
 
@@ -187,8 +190,6 @@ def run_reference_arm(a):
     info = None
     log2n = a.cpu_log2n
     for i in range(a.warmup + a.steps):
-        if i == 1 and times and times[0] > 20.0:             # keep the whole run within a few minutes
-            pass
         gbs, cores, kind, sample, secs = cpu_reference_run(a, log2n)
         info = (cores, kind, sample)
         if i >= a.warmup:
@@ -206,6 +207,135 @@ def run_reference_arm(a):
         "gpu_launches": 0,
     }
     emit(line)
+
+
+# ------------------------------------------------------------------------------------------ sweep
+EBS = (1e-1, 1e-2, 1e-3, 1e-4, 1e-5, 1e-6)
+
+
+def sweep_plan(kind, log2n):
+    """(ct, field, n, eb, chunk) of every extra workload.  BASELINE.json: configs[2] = CT 5/6/11 x absErrorBound 1e-1..1e-6
+    (the loop of impl/experiment.sh:9-19), configs[4] = CT 8/9 on the noisy field, configs[0] = the pingpong shape
+    (131,072 floats, ONE chunk: what impl/pingpong.c:164-169 and :553-566 call), configs[3]'s Himeno face (33,929 floats)."""
+    n = 1 << log2n
+    plan = []
+    if kind == "quick":
+        for ct in (5, 7):
+            for f in ("smooth", "noisy", "constant"):
+                plan.append((ct, f, n, 0.01, 4096))
+        plan.append((5, "smooth", 131072, 0.01, 0))
+        return plan
+    for ct in (5, 6, 7, 11):
+        for f in ("smooth", "noisy", "constant"):
+            plan.append((ct, f, n, 0.01, 4096))
+    for ct in (5, 6, 11):
+        for f in ("smooth", "noisy"):
+            for eb in EBS:
+                if eb != 0.01:
+                    plan.append((ct, f, n, eb, 4096))
+    for ct in (8, 9):
+        for f in ("noisy", "smooth"):
+            plan.append((ct, f, n, 0.01, 4096))
+    for ct in (5, 7):
+        plan.append((ct, "smooth", 1 << 30, 0.01, 4096))
+    for ct in (5, 7, 6, 11):
+        plan.append((ct, "smooth", 131072, 0.01, 0))            # pingpong shape, one chunk (legacy call)
+    plan.append((5, "noisy", 131072, 0.01, 0))
+    plan.append((5, "smooth", 33929, 0.01, 0))                  # Himeno face, size L 2x2x2 (impl/himenoBMTxps.c:644-708)
+    return plan
+
+
+def oracle_check(api, ol, x, comp, out, ct, eb, chunk):
+    """Sampled chunks of the finished round trip against the CPU oracle (stream bytes, CRC, decoded floats).  The oracle is
+    the checker only; nothing here is timed."""
+    n = x.numel()
+    base = 5 if ct == 8 else (7 if ct == 9 else ct)
+    offs = comp.chunk_offsets.cpu().numpy().astype(np.int64)
+    if chunk == 0 or chunk >= n:
+        cs, C = [0], n
+    else:
+        K = offs.size - 1
+        cs, C = sorted(set([0, K // 3, (2 * K) // 3, K - 1])), chunk
+    for c in cs:
+        lo, hi = c * C, min(n, (c + 1) * C)
+        xs = x[lo:hi].cpu().numpy()
+        enc = ol.o_compress_chunked(base, xs, hi - lo, eb, want_crc=ct in (8, 9))
+        got = comp.stream[int(offs[c]):int(offs[c + 1])].cpu().numpy()
+        if got.size != enc["stream"].size or not np.array_equal(got, enc["stream"]):
+            return False
+        if ct in (8, 9) and int(comp.chunk_crc[c].item()) & 0xFFFFFFFF != int(enc["chunk_crc"][0]):
+            return False
+        dec = ol.o_decompress_chunked(base, enc, hi - lo, hi - lo, eb)
+        if not np.array_equal(out[lo:hi].cpu().numpy().view(np.uint32), dec.view(np.uint32)):
+            return False
+    return True
+
+
+def run_sweep(a, dev, world, rank, peak, fields):
+    """-> list of entries; every rank measures its own slice (weak scaling, like the headline), times are max over ranks."""
+    import torch
+    import torch.distributed as dist
+    from data_compression_b200 import api
+    from data_compression_b200.fields import make_field_torch
+    import oracle_lib as ol
+    ol.build_oracle()
+    plan = sweep_plan(a.sweep, a.log2n)
+    rows, times = [], []
+    ws_cache = {}
+    for (ct, field, n, eb, chunk) in plan:
+        key = (field, n)
+        if key not in fields:
+            for k in [k for k in fields if k[1] > (1 << 20)]:                  # one big field at a time
+                del fields[k]
+            for k in [k for k in ws_cache if k[0] != n and k[0] > (1 << 20)]:
+                del ws_cache[k]
+            torch.cuda.empty_cache()
+            fields[key] = make_field_torch(field, n, dev, start=rank * n)
+        x = fields[key]
+        if (n, chunk) not in ws_cache:
+            ws_cache[(n, chunk)] = (api.Workspace(n, chunk, dev), torch.empty(n, dtype=torch.float32, device=dev),
+                                    torch.zeros(1, dtype=torch.int32, device=dev))
+        ws, out, status = ws_cache[(n, chunk)]
+        steps = a.sweep_steps * (4 if n < (1 << 20) else 1)
+        for _ in range(2):
+            comp = api.compress(x, ct=ct, abs_error_bound=eb, chunk_elems=chunk, subtract_min=True, workspace=ws)
+            api.decompress(comp, out=out, status=status)
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
+        torch.cuda.synchronize()
+        for i in range(steps):
+            ev[i][0].record()
+            comp = api.compress(x, ct=ct, abs_error_bound=eb, chunk_elems=chunk, subtract_min=True, workspace=ws)
+            ev[i][1].record()
+            api.decompress(comp, out=out, status=status)
+            ev[i][2].record()
+        torch.cuda.synchronize()
+        tc = float(np.mean([ev[i][0].elapsed_time(ev[i][1]) for i in range(steps)]))
+        td = float(np.mean([ev[i][1].elapsed_time(ev[i][2]) for i in range(steps)]))
+        B = float(comp.total_bytes())
+        ok = bool(status.item() == 0) and oracle_check(api, ol, x, comp, out, ct, eb, chunk)
+        rows.append({"ct": ct, "field": field, "n": n, "eb": eb, "chunk": chunk, "B": B, "ok": ok})
+        times.append([tc, td])
+    tt = torch.tensor(times, dtype=torch.float64, device=dev)
+    tb = torch.tensor([r["B"] for r in rows], dtype=torch.float64, device=dev)
+    okt = torch.tensor([1.0 if r["ok"] else 0.0 for r in rows], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tb, op=dist.ReduceOp.SUM)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+    tt, tb, okt = tt.cpu().numpy(), tb.cpu().numpy(), okt.cpu().numpy()
+    out_rows = []
+    for r, (tc, td), Bsum, okv in zip(rows, tt, tb, okt):
+        n = r["n"]
+        Bg = Bsum / world                                  # stream bytes per GPU
+        out_rows.append({
+            "ct": r["ct"], "field": r["field"], "log2n": round(float(np.log2(n)), 3), "n_per_gpu": n, "eb": r["eb"],
+            "chunk": r["chunk"], "ratio": 4.0 * n / max(Bg, 1.0), "compress_ms": tc, "decompress_ms": td,
+            "input_gbs": 4.0 * n * world / ((tc + td) * 1e-3) / 1e9,
+            "roundtrip_frac_of_hbm": (8.0 * n + 2.0 * Bg) / ((tc + td) * 1e-3) / 1e9 / peak,
+            "compress_frac_of_hbm": (4.0 * n + Bg) / (tc * 1e-3) / 1e9 / peak,
+            "decompress_frac_of_hbm": (4.0 * n + Bg) / (td * 1e-3) / 1e9 / peak,
+            "oracle_check": bool(okv > 0.5)})
+    return out_rows
 
 
 # ------------------------------------------------------------------------------------------ our arm
@@ -360,12 +490,17 @@ def run_ours(a):
                "api": "dcb_compress_host + dcb_decompress_host (blocking C-ABI calls, pinned host buffers, "
                       "%d host thread%s per GPU)" % (T, "" if T == 1 else "s")}
 
+    peak, peak_src = measured_peak()
+    sweep = None
+    if a.sweep != "none":
+        del out
+        sweep = run_sweep(a, dev, world, rank, peak, {(a.field, n): x})
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    peak, peak_src = measured_peak()
     traffic = None                                  # dram bytes per launch of the dominant kernel, from the committed ncu capture
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
@@ -409,6 +544,8 @@ def run_ours(a):
     }
     if e2e:
         line["e2e"] = e2e
+    if sweep is not None:
+        line["sweep"] = sweep
     if world == 1 and not a.no_cpu:
         gbs, cores, kind, sample, _ = cpu_reference_run(a, a.cpu_log2n)
         line["cpu_baseline"] = {"value": gbs, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
