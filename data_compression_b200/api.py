@@ -33,7 +33,7 @@ EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb",
            "dcb_decompress_f64", "dcb_chunk_stats_f64", "dcb_profile_enable", "dcb_profile_last_ms",
            "dcb_hm_length", "dcb_hamming_encode", "dcb_hamming_decode",
            "dcb_bytewise_workspace_bytes", "dcb_bytewise_compress", "dcb_bytewise_decompress",
-           "dcb_bytewise_compress_f64", "dcb_bytewise_decompress_f64"]
+           "dcb_bytewise_compress_f64", "dcb_bytewise_decompress_f64", "dcb_static_max_elems", "dcb_compress_static"]
 
 _lib = None
 
@@ -83,6 +83,9 @@ def lib():
         L.dcb_compress.argtypes = [i32, vp, u64, u64, dbl, u32, i32, u32, vp, u64, vp, vp, vp, vp, vp, vp, u64, vp]
         L.dcb_decompress.restype = i32
         L.dcb_decompress.argtypes = [i32, vp, vp, u64, u64, dbl, u32, i32, u32, vp, vp, vp, vp, vp, vp]
+        L.dcb_static_max_elems.restype = u64
+        L.dcb_compress_static.restype = i32
+        L.dcb_compress_static.argtypes = [i32, vp, u64, u64, dbl, u32, i32, u32, vp, u64, vp, vp, vp, vp, vp, vp]
         L.dcb_crc32_chunks.restype = i32
         L.dcb_crc32_chunks.argtypes = [vp, vp, u64, vp, vp]
         L.dcb_chunk_stats.restype = i32

@@ -326,6 +326,51 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
   return DCB_OK;
 }
 
+// ---- dcb_compress_static: dcb_compress for callers that may not allocate ------------------------------------------------
+// No counterpart in the reference; added (callers under CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  The workspace dcb_compress needs (ticket, group sums, chunk sizes, one
+// 16 KB slot per chunk) lives in a file-scope device array instead of caller memory: every GPU that loads the library holds
+// DCB_STATIC_WS_BYTES until exit.  In HOST code the array's name is only a stand-in, not a device address (a kernel given
+// it faults, or silently uses the wrong memory where the GPU can reach host memory): the address is taken with
+// cudaGetSymbolAddress, once per device, with that device current.  Every call shares the array and it keeps the last
+// call's contents; what must start at zero (header, group sums) is cleared by dcb_compress itself on the caller's stream.
+// Calls that overlap on the GPU (different streams or host threads, same device) RACE on it: serialise them.
+static __device__ __align__(256) unsigned char g_static_ws[DCB_STATIC_WS_BYTES];
+
+static int static_ws_ptr(void** out) {
+  static std::atomic<void*> cache[64];
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { snprintf(g_err, sizeof g_err, "dcb_compress_static: device ordinal %d out of range", dev); return DCB_EINVAL; }
+  void* p = cache[dev].load(std::memory_order_acquire);
+  if (!p) {
+    CK(cudaGetSymbolAddress(&p, g_static_ws));          // the current device's instance of the array
+    cache[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return DCB_OK;
+}
+
+extern "C" uint64_t dcb_static_max_elems(void) { return DCB_STATIC_MAX_ELEMS; }
+
+extern "C" int dcb_compress_static(int ct, const float* d_in, uint64_t n, uint64_t chunk, double eb, uint32_t flags,
+                                   int fixed_type, uint32_t fixed_mask17, uint8_t* d_stream, uint64_t capacity,
+                                   uint64_t* d_offsets, float* d_cmin, float* d_cmed, int32_t* d_ctype, uint32_t* d_ccrc,
+                                   void* stream) {
+  if (dcb_device_count() == 0) return DCB_ENODEVICE;
+  const uint64_t need = dcb_workspace_bytes(n, chunk);
+  if (n > DCB_STATIC_MAX_ELEMS || need > DCB_STATIC_WS_BYTES) {
+    snprintf(g_err, sizeof g_err, "dcb_compress_static: n = %llu elements needs %llu bytes of scratch; the static array holds %llu "
+             "(at most %llu elements per call) -- use dcb_compress with caller memory", (unsigned long long)n,
+             (unsigned long long)need, (unsigned long long)DCB_STATIC_WS_BYTES, (unsigned long long)DCB_STATIC_MAX_ELEMS);
+    return DCB_ECAPACITY;
+  }
+  void* ws = nullptr;
+  { int rc_ = static_ws_ptr(&ws); if (rc_) return rc_; }
+  return dcb_compress(ct, d_in, n, chunk, eb, flags, fixed_type, fixed_mask17, d_stream, capacity, d_offsets, d_cmin, d_cmed,
+                      d_ctype, d_ccrc, ws, DCB_STATIC_WS_BYTES, stream);
+}
+
 template <int CT>
 static cudaError_t launch_decode(const DecArgs& a, cudaStream_t st) {
   // (the attribute is per device, and setting it is cheap: no process-wide "already set" flag)

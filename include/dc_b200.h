@@ -71,6 +71,21 @@ int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chunk_elems, do
                  float* d_chunk_min, float* d_chunk_medium, int32_t* d_chunk_type, uint32_t* d_chunk_crc,
                  void* d_workspace, uint64_t workspace_bytes, void* cuda_stream);
 
+/* dcb_compress without caller-provided scratch and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, serving loops).  The workspace is
+ * a static device array inside the library (DCB_STATIC_WS_BYTES on every GPU that loads it); n is limited to
+ * DCB_STATIC_MAX_ELEMS elements per call (larger n: DCB_ECAPACITY, text in dcb_last_cuda_error).  All calls on one device
+ * share that array, so calls that overlap on the GPU race: issue them on one stream or order them with events.
+ * Results are those of dcb_compress, bit for bit. */
+#define DCB_STATIC_MAX_ELEMS (1ull << 20)
+#define DCB_STATIC_WS_BYTES ((1ull << 22) + (1ull << 16))   /* 256 slots of 16 KB + tables of 2^20 elements, rounded up */
+uint64_t dcb_static_max_elems(void);
+int dcb_compress_static(int ct, const float* d_in, uint64_t n, uint64_t chunk_elems, double abs_error_bound,
+                        uint32_t flags, int fixed_type, uint32_t fixed_mask17,
+                        uint8_t* d_stream, uint64_t stream_capacity, uint64_t* d_chunk_offsets,
+                        float* d_chunk_min, float* d_chunk_medium, int32_t* d_chunk_type, uint32_t* d_chunk_crc,
+                        void* cuda_stream);
+
 /* Mirror of dcb_compress: decodes exactly n values (chunk c holds min(chunk_elems, n - c*chunk_elems)).
  * d_stream must be readable up to the next multiple of 4 bytes past d_chunk_offsets[K].
  * d_status (device int32, may be NULL) receives DCB_OK / DCB_EFORMAT. */
