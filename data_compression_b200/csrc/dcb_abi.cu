@@ -14,6 +14,7 @@
 #include "dcb_encode_slots.cuh"
 #include "dcb_encode_warp.cuh"
 #include "dcb_decode.cuh"
+#include "dcb_decode_single.cuh"
 #include "dcb_stats.cuh"
 #include "dcb_crc.cuh"
 #include "dcb_face.cuh"
@@ -371,6 +372,35 @@ extern "C" int dcb_compress_static(int ct, const float* d_in, uint64_t n, uint64
                       d_ctype, d_ccrc, ws, DCB_STATIC_WS_BYTES, stream);
 }
 
+// Stream-ordered scratch of the single-chunk decoder: the library's own memory pool per device, which keeps what it has
+// been given (release threshold = max) -- with the default pool's threshold of 0 every call paid a real allocation.
+static int scratch_pool(cudaMemPool_t* out) {
+  static std::atomic<cudaMemPool_t> pools[64];
+  static std::mutex mu;
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return DCB_EINVAL;
+  cudaMemPool_t p = pools[dev].load(std::memory_order_acquire);
+  if (!p) {
+    std::lock_guard<std::mutex> lk(mu);
+    p = pools[dev].load(std::memory_order_acquire);
+    if (!p) {
+      cudaMemPoolProps props;
+      memset(&props, 0, sizeof props);
+      props.allocType = cudaMemAllocationTypePinned;
+      props.handleTypes = cudaMemHandleTypeNone;
+      props.location.type = cudaMemLocationTypeDevice;
+      props.location.id = dev;
+      CK(cudaMemPoolCreate(&p, &props));
+      uint64_t keep = ~0ull;
+      CK(cudaMemPoolSetAttribute(p, cudaMemPoolAttrReleaseThreshold, &keep));
+      pools[dev].store(p, std::memory_order_release);
+    }
+  }
+  *out = p;
+  return DCB_OK;
+}
+
 template <int CT>
 static cudaError_t launch_decode(const DecArgs& a, cudaStream_t st) {
   // (the attribute is per device, and setting it is cheap: no process-wide "already set" flag)
@@ -405,6 +435,26 @@ extern "C" int dcb_decompress(int ct, const uint8_t* d_stream, const uint64_t* d
   a.flags = flags & 7u; a.fixed_type = fixed_type; a.fixed_mask17 = fixed_mask17;
   a.cmin = d_cmin; a.cmed = d_cmed; a.ctype = d_ctype; a.out = d_out; a.status = d_status;
   cudaError_t e;
+  // ONE chunk of more than a tile (the reference's own call shape): codes are located and resolved in parallel inside the
+  // chunk (dcb_decode_single.cuh) instead of by one lane.  Its scratch (a byte per element + tables) is stream-ordered
+  // memory: allocated and freed on `st`, no host synchronisation.  DCB_DECODER=lane keeps the lane-per-chunk kernel.
+  static const bool lane_only = [] { const char* v = getenv("DCB_DECODER"); return v && !strcmp(v, "lane"); }();
+  if (a.num_chunks == 1 && n > DCB_TILE && !lane_only) {
+    void* ws = nullptr;
+    cudaMemPool_t pool = nullptr;
+    { int rc_ = scratch_pool(&pool); if (rc_) return rc_; }
+    CK(cudaMallocFromPoolAsync(&ws, (size_t)ds_workspace_bytes(n), pool, st));
+    switch (bct) {
+      case CT_BITWISE: e = ds_launch<CT_BITWISE>(a, ws, st); break;
+      case CT_NP: e = ds_launch<CT_NP>(a, ws, st); break;
+      case CT_MASK: e = ds_launch<CT_MASK>(a, ws, st); break;
+      default: e = ds_launch<CT_OP>(a, ws, st); break;
+    }
+    cudaError_t ef = cudaFreeAsync(ws, st);
+    CK(e);
+    CK(ef);
+    return DCB_OK;
+  }
   switch (bct) {
     case CT_BITWISE: e = launch_decode<CT_BITWISE>(a, st); break;
     case CT_NP: e = launch_decode<CT_NP>(a, st); break;
