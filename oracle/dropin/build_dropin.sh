@@ -33,7 +33,10 @@ $CC -o "$OUT/pingpong_ref" "$OUT/pingpong.o" "$OUT/dataCompression.o" "$OUT/mpis
 tmp="$OUT/.himeno.$$"
 mkdir -p "$tmp"
 (cd "$tmp" && sh "$REF/paramset.sh" S 1 1 1 >/dev/null && cp "$HERE/mpi.h" . &&
+ $CC -x c -O3 -ffp-contract=off -fPIC -w -I. -I"$REF" -c -o dc_S.o - < "$REF/dataCompression.c" &&
+ $CC -O3 -fPIC -w -I. -c -o mpistub_pic.o "$HERE/mpistub.c" &&
  (echo '#define main himeno_main'; cat "$REF/himenoBMTxps.c"; echo; echo '#undef main'; cat "$HERE/himeno_access.c") |
- $CC -x c -O3 -ffp-contract=off -fPIC -shared -w -I. -I"$REF" -o "$OUT/libhimeno_ref.so" - "$HERE/mpistub.c" "$REF/dataCompression.c" -lm -lz)
+ $CC -x c -O3 -ffp-contract=off -fPIC -w -I. -I"$REF" -c -o himeno_S.o - &&
+ $CC -shared -o "$OUT/libhimeno_ref.so" himeno_S.o dc_S.o mpistub_pic.o -lm -lz)
 rm -rf "$tmp"
 echo "built $OUT"
