@@ -74,6 +74,45 @@ def exchange_axis(p, ijk, imax, jmax, kmax, lo_peer, hi_peer, ct=5, eb=0.01, com
     return (out_lo.stream.numel() if out_lo is not None else 0) + (out_hi.stream.numel() if out_hi is not None else 0)
 
 
+def exchange_axis_fixed(p, ijk, imax, jmax, kmax, lo_peer, hi_peer, ct=5, eb=0.01, chunk_elems=0, compressed_cls=None):
+    """exchange_axis with fixed-capacity frames (transport.pack_fixed): ONE batched isend/irecv round per axis and no host
+    round trip -- the announced stream length stays on the device.  chunk_elems = 0 compresses a face as ONE reference call
+    (the shape of impl/himenoBMTxps.c:644-708); chunk_elems = 4096 makes every 4096 values of the face a reference call of
+    their own, which lets the receiver decode the chunks side by side (a face of predicted codes only is otherwise one dependent
+    chain).  Returns the frame bytes sent."""
+    import torch
+    import torch.distributed as dist
+    cls = compressed_cls or api.Compressed
+    ext = {1: imax, 2: jmax, 3: kmax}[ijk]
+    n = {1: jmax * kmax, 2: imax * kmax, 3: imax * jmax}[ijk]
+    dev = p.device
+    fb = tr.fixed_frame_bytes(n, chunk_elems)
+
+    def comp_face(v):
+        face = api.gather_face(p, ijk, v, imax, jmax, kmax)
+        return tr.pack_fixed(api.compress(face, ct=ct, abs_error_bound=eb, chunk_elems=chunk_elems, subtract_min=True))
+
+    out_lo = comp_face(1) if lo_peer is not None else None
+    out_hi = comp_face(ext - 2) if hi_peer is not None else None
+    in_hi = torch.empty(fb, dtype=torch.uint8, device=dev) if hi_peer is not None else None
+    in_lo = torch.empty(fb, dtype=torch.uint8, device=dev) if lo_peer is not None else None
+    ops = []
+    if out_lo is not None: ops.append(dist.P2POp(dist.isend, out_lo, lo_peer))
+    if out_hi is not None: ops.append(dist.P2POp(dist.isend, out_hi, hi_peer))
+    if in_hi is not None: ops.append(dist.P2POp(dist.irecv, in_hi, hi_peer))
+    if in_lo is not None: ops.append(dist.P2POp(dist.irecv, in_lo, lo_peer))
+    if not ops:
+        return 0
+    for w in dist.batch_isend_irecv(ops):
+        w.wait()
+    flags = api.F_SUBTRACT_MIN
+    if in_hi is not None:
+        write_face(p, ijk, ext - 1, imax, jmax, kmax, tr.unpack_fixed(in_hi, n, chunk_elems, ct, eb, flags, cls))
+    if in_lo is not None:
+        write_face(p, ijk, 0, imax, jmax, kmax, tr.unpack_fixed(in_lo, n, chunk_elems, ct, eb, flags, cls))
+    return fb * ((out_lo is not None) + (out_hi is not None))
+
+
 def exchange_axis_raw(p, ijk, imax, jmax, kmax, lo_peer, hi_peer):
     """CT=0: the uncompressed faces (the reference's MPI vector types, impl/himenoBMTxps.c sendp1/2/3 default branch) -- one
     batched round of float32 faces.  Returns the bytes sent."""

@@ -242,3 +242,79 @@ def bcast_compressed(comp, root, n, chunk_elems, device, compressed_cls, f64=Fal
                 dist.recv(got.stream[:total], root, group=group)   # :1062-1065
             resends = 1
     return got, resends
+
+
+# ---- fixed-capacity frames: one message per hop, no host round trip ------------------------------------------------------
+# The two-message hop above reads the announced stream length on the host (a device synchronisation per hop), which is what a
+# hop of a 66-136 KB Himeno face or of the 131,072-float pingpong array costs most over NVLink.  Both ends know n and
+# chunk_elems, hence the worst-case frame size: [table int64 words][stream capacity 4n + 16 bytes] goes out as ONE buffer of
+# that size.  The length travels inside the table (word 7) and stays on the device; the unused tail of
+# the stream region is never read by the decoder.  Meant for latency-bound payloads (default: frames up to 4 MiB); a large
+# array keeps the two-message hop, whose second message has the compressed length.
+FIXED_FRAME_MAX_BYTES = 4 << 20
+
+
+def fixed_frame_bytes(n, chunk_elems):
+    K = num_chunks(n, chunk_elems)
+    return 8 * table_words(K) + ((4 * n + 16 + 15) // 16) * 16
+
+
+def use_fixed_frame(n, chunk_elems):
+    return fixed_frame_bytes(n, chunk_elems) <= FIXED_FRAME_MAX_BYTES
+
+
+def pack_fixed(comp):
+    """comp (float32 api.Compressed) -> one uint8 tensor of fixed_frame_bytes(n, chunk_elems); no host synchronisation."""
+    import torch
+    K = comp.chunk_offsets.numel() - 1
+    dev = comp.stream.device
+    tw = table_words(K)
+    buf = torch.empty(fixed_frame_bytes(comp.n, comp.chunk_elems), dtype=torch.uint8, device=dev)
+    t = buf[:8 * tw].view(torch.int64)
+    eb_bits = int(np.array([comp.abs_error_bound], dtype=np.float64).view(np.int64)[0])
+    hdr = [MAGIC, comp.ct, comp.n, comp.chunk_elems, eb_bits, (comp.flags & 0xFF) | ((comp.fixed_type & 0xFF) << 8),
+           comp.fixed_mask17, 0]
+    t[:HEADER_WORDS] = torch.tensor(hdr, dtype=torch.int64).to(dev, non_blocking=True)
+    t[HEADER_WORDS:HEADER_WORDS + K + 1] = comp.chunk_offsets
+    t[HEADER_WORDS - 1:HEADER_WORDS] = comp.chunk_offsets[K:K + 1]          # total bytes, device to device
+    side = t[HEADER_WORDS + K + 1:].view(torch.int32)
+    side.zero_()
+    for i, f in enumerate((comp.chunk_min, comp.chunk_medium, comp.chunk_type, comp.chunk_crc)):
+        if f is not None:
+            side[i * K:(i + 1) * K] = f[:K].view(torch.int32)
+    cap = buf.numel() - 8 * tw
+    buf[8 * tw:] = comp.stream[:cap]
+    return buf
+
+
+def unpack_fixed(buf, n, chunk_elems, ct, abs_error_bound, flags, compressed_cls, fixed_type=0, fixed_mask17=0):
+    """Views into a received fixed frame.  The codec parameters are the receiver's own (both ends of a pingpong / halo hop
+    run the same configuration): nothing is read back to the host."""
+    import torch
+    K = num_chunks(n, chunk_elems)
+    tw = table_words(K)
+    t = buf[:8 * tw].view(torch.int64)
+    offs = t[HEADER_WORDS:HEADER_WORDS + K + 1]
+    side = t[HEADER_WORDS + K + 1:].view(torch.int32)
+    per_chunk_mask = ct in (7, 9) and not (flags & 2)
+    has_crc = bool(flags & 4) or ct in (8, 9)
+    return compressed_cls(ct, n, chunk_elems, abs_error_bound, flags, fixed_type, fixed_mask17, buf[8 * tw:], offs,
+                          side[0:K].view(torch.float32) if (flags & 1) else None,
+                          side[K:2 * K].view(torch.float32) if per_chunk_mask else None,
+                          side[2 * K:3 * K] if per_chunk_mask else None,
+                          side[3 * K:4 * K] if has_crc else None)
+
+
+def send_fixed(comp, dst, group=None):
+    import torch.distributed as dist
+    buf = pack_fixed(comp)
+    dist.send(buf, dst, group=group)
+    return buf
+
+
+def recv_fixed(n, chunk_elems, src, device, ct, abs_error_bound, flags, compressed_cls, group=None, buffer=None):
+    import torch
+    import torch.distributed as dist
+    buf = buffer if buffer is not None else torch.empty(fixed_frame_bytes(n, chunk_elems), dtype=torch.uint8, device=device)
+    dist.recv(buf, src, group=group)
+    return unpack_fixed(buf, n, chunk_elems, ct, abs_error_bound, flags, compressed_cls)
