@@ -39,6 +39,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
+ALL_CPUS = os.sched_getaffinity(0)           # before run_ours narrows the affinity to the GPU's NUMA node
 METRIC = "compress+decompress input GB/s"
 UNIT = "GB/s"
 
@@ -60,6 +61,7 @@ def parse_args():
     ap.add_argument("--sweep", default="full", choices=("full", "quick", "none"),
                     help="extra workloads measured after the headline and reported under \"sweep\" (BASELINE.json configs 1, 3, 5)")
     ap.add_argument("--sweep-steps", type=int, default=5)
+    ap.add_argument("--no-nccl", action="store_true", help="skip the pingpong / Himeno NCCL sub-records at --gpus >= 2")
     ap.add_argument("--cpu-log2n", type=int, default=28, help="bounded CPU sample = 2^cpu_log2n elements (default: the whole per-GPU field, ~15 s of CPU work over 16 cores)")
     return ap.parse_args()
 
@@ -164,14 +166,21 @@ def cpu_reference_run(a, log2n, start=0):
     import oracle_lib as ol
     ol.build_oracle()
     use_ref = ol.ref_available(a.eb)
-    cores = os.cpu_count() or 1
+    if use_ref:
+        ol.RefLib(a.eb)                      # dlopen oracle/_ref/libdcref_<eb>.so in the parent: the forked workers inherit it
+    cores = len(ALL_CPUS) or 1
     n = 1 << log2n
     per = max(a.chunk, (n // cores) // a.chunk * a.chunk)
     jobs = [(a.field, start + lo, min(per, n - lo), a.chunk, a.ct, a.eb, use_ref) for lo in range(0, n, per)]
     ctx = mp.get_context("fork")
+    narrowed = os.sched_getaffinity(0)
+    os.sched_setaffinity(0, ALL_CPUS)            # the CPU baseline gets every host core (forked workers inherit the mask)
     t0 = time.perf_counter()
-    with ctx.Pool(min(cores, len(jobs))) as pool:
-        res = pool.map(_ref_worker, jobs)
+    try:
+        with ctx.Pool(min(cores, len(jobs))) as pool:
+            res = pool.map(_ref_worker, jobs)
+    finally:
+        os.sched_setaffinity(0, narrowed)
     wall = time.perf_counter() - t0
     busy = max(r[0] for r in res)
     gbs = 4.0 * n / busy / 1e9
@@ -201,7 +210,8 @@ def run_reference_arm(a):
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": 1e3 * float(np.mean(times)), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32/u32", "data": "synthetic",
-        "config": {"workload": workload_name(a), "sample": sample},
+        "config": {"workload": workload_name(a), "ct": a.ct, "field": a.field, "n_per_gpu": 1 << a.log2n,
+                   "abs_error_bound": a.eb, "chunk_elems": a.chunk, "sample": sample},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -338,6 +348,142 @@ def run_sweep(a, dev, world, rank, peak, fields):
     return out_rows
 
 
+# ------------------------------------------------------------------------------------------ NCCL sub-records (N >= 2)
+def nccl_records(a, dev, rank, world):
+    """Compressed payloads moving between GPUs with NCCL send/recv (BASELINE.json configs[0] and configs[3]): the pingpong hop
+    of impl/pingpong.c:226-611 between rank pairs, and the Himeno solver with compressed k-faces (impl/himenoBMTxps.c:247-299,
+    :644-708) on all ranks.  Times are CUDA events, max over ranks."""
+    import importlib.util
+    import torch
+    import torch.distributed as dist
+    from data_compression_b200 import api, transport as tr
+    from data_compression_b200.fields import make_field_torch
+    peer = rank ^ 1
+    paired = peer < world
+    sender_first = (rank & 1) == 0
+
+    def timed(fn, reps):
+        fn()
+        torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize(); dist.barrier()
+        t = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    pp = []
+    for name, field, n, chunk, reps in (("pingpong 131072 (float_eq shape, one chunk)", "constant", 131072, 0, 50),
+                                        ("pingpong 131072 smooth (one chunk)", "smooth", 131072, 0, 50),
+                                        ("pingpong 2^24 smooth (chunk 4096)", "smooth", 1 << 24, 4096, 10)):
+        x = make_field_torch(field, n, dev, start=0)
+        ws = api.Workspace(n, chunk, dev)
+        out = torch.empty(n, dtype=torch.float32, device=dev)
+        rec = {"case": name, "n": n, "chunk": chunk, "field": field}
+        xr = torch.empty_like(x)
+
+        def hop_raw():                                          # CT=0: impl/pingpong.c:233 / :336
+            if not paired:
+                return
+            if sender_first:
+                dist.send(x, peer); dist.recv(xr, peer)
+            else:
+                dist.recv(xr, peer); dist.send(x, peer)
+        rec["ct0_round_trip_us"] = 1e3 * timed(hop_raw, reps)
+        for ct in (5, 8):
+            fixed = tr.use_fixed_frame(n, chunk)
+            cws = tr.FrameWorkspace(n, chunk, dev, ct=ct) if fixed else ws        # the codec writes straight into the frame
+            comp = api.compress(x, ct=ct, abs_error_bound=0.01, chunk_elems=chunk, subtract_min=True, workspace=cws)
+            flags = comp.flags | (4 if ct == 8 else 0)
+            got_box = [None]
+            rbuf = torch.empty(tr.fixed_frame_bytes(n, chunk), dtype=torch.uint8, device=dev) if fixed else None
+
+            def hop():
+                if not paired:
+                    return
+                if fixed:
+                    if sender_first:
+                        dist.send(cws.frame, peer)
+                        got_box[0] = tr.recv_fixed(n, chunk, peer, dev, ct, 0.01, flags, api.Compressed, buffer=rbuf)
+                    else:
+                        got_box[0] = tr.recv_fixed(n, chunk, peer, dev, ct, 0.01, flags, api.Compressed, buffer=rbuf)
+                        dist.send(cws.frame, peer)
+                else:
+                    if sender_first:
+                        tr.send_compressed(comp, peer); got_box[0] = tr.recv_compressed(n, chunk, peer, dev, api.Compressed)
+                    else:
+                        got_box[0] = tr.recv_compressed(n, chunk, peer, dev, api.Compressed); tr.send_compressed(comp, peer)
+            rec["ct%d_round_trip_us" % ct] = 1e3 * timed(hop, reps)
+            rec["ct%d_frame" % ct] = "fixed-capacity, one message" if fixed else "table + stream, two messages"
+            rec["ct%d_compress_us" % ct] = 1e3 * timed(lambda: api.compress(x, ct=ct, abs_error_bound=0.01, chunk_elems=chunk,
+                                                                              subtract_min=True, workspace=cws), reps)
+            ok = True
+            if paired:
+                got = got_box[0]
+                rec["ct%d_decompress_us" % ct] = 1e3 * timed(lambda: api.decompress(got, out=out), reps)
+                K = got.chunk_offsets.numel() - 1
+                ok = bool(torch.equal(out, api.decompress(comp)))        # both ranks hold the same field: the peer's array decodes to mine
+                if ct == 8:                                              # receiver side of impl/pingpong.c:380-410
+                    crc = api.crc32_chunks(got.stream, got.chunk_offsets)
+                    ok = ok and bool(torch.equal(crc[:K].view(torch.int32), got.chunk_crc[:K].view(torch.int32)))
+            else:
+                timed(lambda: None, 1)
+            okt = torch.tensor([1 if ok else 0], device=dev)
+            dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+            rec["ct%d_check" % ct] = bool(okt.item())
+            rec["ct%d_bytes" % ct] = int(comp.total_bytes())
+        pp.append(rec)
+        del x, ws, out, xr
+
+    spec = importlib.util.spec_from_file_location("himeno_nccl", os.path.join(ROOT, "examples", "himeno_nccl.py"))
+    hm = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(hm)
+    m, nn, eb = 257, 20, 1e-4                                   # size L faces: 257 x 257 = 66,049 values
+    him = {"grid": "%dx%dx%d on %d ranks (chain along k)" % (m, m, world * (m - 2) + 2, world), "nn": nn, "abs_error_bound": eb}
+    base = None
+    for label, ct, mode in (("ct0", 0, "fixed"), ("ct5_one_call_per_face", 5, "fixed"), ("ct5_chunked_4096", 5, "fixed_chunked"),
+                            ("ct5_two_rounds_r1", 5, "two_round")):
+        import argparse as _ap
+        args = _ap.Namespace(size=m, eb=eb, nn=nn, mode=mode)
+        hm.run(_ap.Namespace(size=m, eb=eb, nn=2, mode=mode), ct, rank, world, dev)
+        blk, gosa, sent, ms = hm.run(args, ct, rank, world, dev)
+        him[label + "_ms_per_iter"] = ms / nn
+        him[label + "_gosa"] = gosa
+        him[label + "_halo_bytes_rank0"] = sent
+        if ct == 0:
+            base = blk.p.clone()
+        else:
+            d = torch.tensor([float((blk.p - base).abs().max().item())], dtype=torch.float64, device=dev)
+            dist.all_reduce(d, op=dist.ReduceOp.MAX)
+            him[label + "_max_dev_from_ct0"] = float(d.item())
+            him[label + "_within_nn_eb"] = bool(d.item() <= nn * eb)
+    return {"pingpong": pp, "himeno": him}
+
+
+def bind_to_gpu_numa_node(index):
+    """CPU affinity of this process = the cores NVML reports next to GPU `index` (pinned host buffers then land on that NUMA
+    node, and the copy threads run there).  Returns the number of CPUs, or None when NVML does not say."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(vis.split(",")[index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else index
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
 # ------------------------------------------------------------------------------------------ our arm
 def run_ours(a):
     import torch
@@ -352,6 +498,7 @@ def run_ours(a):
         raise SystemExit("bench.py: no CUDA device (the product has no CPU path)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    affinity = bind_to_gpu_numa_node(local)       # before any pinned allocation: first touch places the pages
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     api.lib()
@@ -445,27 +592,43 @@ def run_ours(a):
         reps = max(2, min(a.steps, 5))
         encs, errs = [None] * T, []
 
-        def round_trips(t, count):
-            # odd threads start with the decompress of their warm-up result, so that one thread's host->device copy runs
-            # against the other's device->host copy instead of both pulling in the same direction at the same time
+        # worker threads live across warm-up and timed repetitions (the library caches device buffers per host thread; a
+        # thread that exits gives them back), stepped by barriers
+        gate = threading.Barrier(T + 1)
+        plan = {"count": 0, "stop": False}
+
+        def worker(t):
             try:
                 torch.cuda.set_device(dev)                  # the current CUDA device is per host thread
-                for _ in range(count):
-                    if t % 2 == 1 and encs[t] is not None:
-                        api.decompress_host(encs[t], out=ohs[t].numpy())
-                    encs[t] = api.compress_host(xnp, ct=a.ct, abs_error_bound=a.eb, chunk_elems=a.chunk,
-                                                out={"stream": shs[t].numpy()})
-                    if not (t % 2 == 1 and count == reps):
-                        api.decompress_host(encs[t], out=ohs[t].numpy())
+                while True:
+                    gate.wait()
+                    if plan["stop"]:
+                        break
+                    count = plan["count"]
+                    # odd threads start with the decompress of their warm-up result, so that one thread's host->device copy
+                    # runs against the other's device->host copy instead of both pulling in the same direction
+                    for _ in range(count):
+                        if t % 2 == 1 and encs[t] is not None:
+                            api.decompress_host(encs[t], out=ohs[t].numpy())
+                        encs[t] = api.compress_host(xnp, ct=a.ct, abs_error_bound=a.eb, chunk_elems=a.chunk,
+                                                    out={"stream": shs[t].numpy()})
+                        if not (t % 2 == 1 and count == reps):
+                            api.decompress_host(encs[t], out=ohs[t].numpy())
+                    gate.wait()
             except Exception as e:  # pragma: no cover
                 errs.append(e)
+                gate.abort()
+            finally:
+                api.lib().dcb_host_release()
+
+        ths = [threading.Thread(target=worker, args=(t,)) for t in range(T)]
+        for th in ths:
+            th.start()
 
         def run(count):
-            ths = [threading.Thread(target=round_trips, args=(t, count)) for t in range(T)]
-            for th in ths:
-                th.start()
-            for th in ths:
-                th.join()
+            plan["count"] = count
+            gate.wait()                                     # go
+            gate.wait()                                     # done
             if errs:
                 raise errs[0]
 
@@ -475,6 +638,10 @@ def run_ours(a):
         run(reps)
         barrier()
         te = (time.perf_counter() - te0) / (reps * T)
+        plan["stop"] = True
+        gate.wait()
+        for th in ths:
+            th.join()
         tmax = torch.tensor([te], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -486,15 +653,66 @@ def run_ours(a):
         e2e = {"value": 4.0 * n * world / te / 1e9, "unit": UNIT,
                "h2d_bytes_per_step": int(4 * n + enc["total_bytes"] + tables),
                "d2h_bytes_per_step": int(4 * n + enc["total_bytes"] + tables),
-               "ms_per_step": 1e3 * te, "host_threads": T,
+               "ms_per_step": 1e3 * te, "host_threads": T, "cpu_affinity_cpus": affinity,
                "api": "dcb_compress_host + dcb_decompress_host (blocking C-ABI calls, pinned host buffers, "
                       "%d host thread%s per GPU)" % (T, "" if T == 1 else "s")}
+        # ---- what ONE caller gets: the strictly serial call sequence of a reference driver (compress, then decompress, one
+        #      thread), with pinned buffers and with plain malloc'd (pageable) ones, as impl/pingpong.c would pass them
+        def serial(xin, sbuf, obuf, k):
+            api.decompress_host(api.compress_host(xin, ct=a.ct, abs_error_bound=a.eb, chunk_elems=a.chunk, out={"stream": sbuf}), out=obuf)
+            barrier()
+            t0_ = time.perf_counter()
+            for _ in range(k):
+                api.decompress_host(api.compress_host(xin, ct=a.ct, abs_error_bound=a.eb, chunk_elems=a.chunk, out={"stream": sbuf}), out=obuf)
+            barrier()
+            tt_ = torch.tensor([(time.perf_counter() - t0_) / k], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tt_, op=dist.ReduceOp.MAX)
+            return 4.0 * n * world / float(tt_.item()) / 1e9
+        e2e["serial_pinned_gbs"] = serial(xnp, shs[0].numpy(), ohs[0].numpy(), 2)
+        xpg = np.empty(n, dtype=np.float32); xpg[:] = xnp
+        e2e["serial_pageable_gbs"] = serial(xpg, np.empty(shs[0].numel(), dtype=np.uint8), np.empty(n, dtype=np.float32), 2)
+        api.lib().dcb_host_release()
+        # ---- the box's ceiling for this traffic: all ranks copy 4n + B bytes host->device and device->host at the same
+        #      time (plain cudaMemcpyAsync on two streams, pinned buffers); a round trip moves exactly that much each way
+        B_ = int(enc["total_bytes"])
+        nb = 4 * n + B_
+        hsrc = torch.empty(nb, dtype=torch.uint8).pin_memory()
+        hdst = torch.empty(nb, dtype=torch.uint8).pin_memory()
+        dsrc = torch.empty(nb, dtype=torch.uint8, device=dev)
+        ddst = torch.empty(nb, dtype=torch.uint8, device=dev)
+        s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+        def both():
+            with torch.cuda.stream(s1):
+                ddst.copy_(hsrc, non_blocking=True)
+            with torch.cuda.stream(s2):
+                hdst.copy_(dsrc, non_blocking=True)
+            s1.synchronize(); s2.synchronize()
+        both()
+        barrier()
+        t0_ = time.perf_counter()
+        for _ in range(3):
+            both()
+        barrier()
+        tc_ = torch.tensor([(time.perf_counter() - t0_) / 3], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tc_, op=dist.ReduceOp.MAX)
+        ceil_gbs = 4.0 * n * world / float(tc_.item()) / 1e9
+        e2e["ceiling"] = {"input_gbs": ceil_gbs, "per_direction_gbs_per_gpu": nb / float(tc_.item()) / 1e9,
+                          "how": "every rank copies 4n+B bytes H2D and D2H concurrently (cudaMemcpyAsync, pinned, two streams)"}
+        e2e["frac_of_ceiling"] = e2e["value"] / ceil_gbs
+        del hsrc, hdst, dsrc, ddst
 
     peak, peak_src = measured_peak()
     sweep = None
     if a.sweep != "none":
         del out
         sweep = run_sweep(a, dev, world, rank, peak, {(a.field, n): x})
+
+    nccl = None
+    if world > 1 and not a.no_nccl:
+        nccl = nccl_records(a, dev, rank, world)
 
     if rank != 0:
         if world > 1:
@@ -546,6 +764,9 @@ def run_ours(a):
         line["e2e"] = e2e
     if sweep is not None:
         line["sweep"] = sweep
+    if nccl is not None:
+        line["pingpong"] = nccl["pingpong"]
+        line["himeno"] = nccl["himeno"]
     if world == 1 and not a.no_cpu:
         gbs, cores, kind, sample, _ = cpu_reference_run(a, a.cpu_log2n)
         line["cpu_baseline"] = {"value": gbs, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}

@@ -33,7 +33,7 @@ EXPORTS = ["dcb_version", "dcb_last_cuda_error", "dcb_device_count", "dcb_n_eb",
            "dcb_decompress_f64", "dcb_chunk_stats_f64", "dcb_profile_enable", "dcb_profile_last_ms",
            "dcb_hm_length", "dcb_hamming_encode", "dcb_hamming_decode",
            "dcb_bytewise_workspace_bytes", "dcb_bytewise_compress", "dcb_bytewise_decompress",
-           "dcb_bytewise_compress_f64", "dcb_bytewise_decompress_f64", "dcb_static_max_elems", "dcb_compress_static"]
+           "dcb_bytewise_compress_f64", "dcb_bytewise_decompress_f64", "dcb_static_max_elems", "dcb_compress_static", "dcb_host_release"]
 
 _lib = None
 

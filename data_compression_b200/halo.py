@@ -5,6 +5,7 @@ decompress, add the sender's min and write the halo planes.  Absent neighbours (
 from . import api, transport as tr
 
 AXIS_DIM = {1: 0, 2: 1, 3: 2}
+_FRAMES, _INBUFS = {}, {}            # exchange_axis_fixed: frame workspaces / receive buffers, reused from call to call
 
 
 def compress_face(p, ijk, v, imax, jmax, kmax, ct, eb):
@@ -88,14 +89,27 @@ def exchange_axis_fixed(p, ijk, imax, jmax, kmax, lo_peer, hi_peer, ct=5, eb=0.0
     dev = p.device
     fb = tr.fixed_frame_bytes(n, chunk_elems)
 
-    def comp_face(v):
+    def comp_face(v, slot):
+        # the codec writes table and stream straight into the frame (transport.FrameWorkspace): nothing to pack
+        key = (n, chunk_elems, ct, eb, str(dev), slot)
+        ws = _FRAMES.get(key)
+        if ws is None:
+            ws = _FRAMES[key] = tr.FrameWorkspace(n, chunk_elems, dev, ct=ct, abs_error_bound=eb)
         face = api.gather_face(p, ijk, v, imax, jmax, kmax)
-        return tr.pack_fixed(api.compress(face, ct=ct, abs_error_bound=eb, chunk_elems=chunk_elems, subtract_min=True))
+        api.compress(face, ct=ct, abs_error_bound=eb, chunk_elems=chunk_elems, subtract_min=True, workspace=ws)
+        return ws.frame
 
-    out_lo = comp_face(1) if lo_peer is not None else None
-    out_hi = comp_face(ext - 2) if hi_peer is not None else None
-    in_hi = torch.empty(fb, dtype=torch.uint8, device=dev) if hi_peer is not None else None
-    in_lo = torch.empty(fb, dtype=torch.uint8, device=dev) if lo_peer is not None else None
+    def in_buf(slot):
+        key = (fb, str(dev), slot)
+        b = _INBUFS.get(key)
+        if b is None:
+            b = _INBUFS[key] = torch.empty(fb, dtype=torch.uint8, device=dev)
+        return b
+
+    out_lo = comp_face(1, 0) if lo_peer is not None else None
+    out_hi = comp_face(ext - 2, 1) if hi_peer is not None else None
+    in_hi = in_buf(0) if hi_peer is not None else None
+    in_lo = in_buf(1) if lo_peer is not None else None
     ops = []
     if out_lo is not None: ops.append(dist.P2POp(dist.isend, out_lo, lo_peer))
     if out_hi is not None: ops.append(dist.P2POp(dist.isend, out_hi, hi_peer))

@@ -254,9 +254,13 @@ def bcast_compressed(comp, root, n, chunk_elems, device, compressed_cls, f64=Fal
 FIXED_FRAME_MAX_BYTES = 4 << 20
 
 
+def _fixed_table_bytes(K):
+    return ((8 * table_words(K) + 15) // 16) * 16              # the stream region starts 16-byte aligned (dcb_decompress needs it)
+
+
 def fixed_frame_bytes(n, chunk_elems):
     K = num_chunks(n, chunk_elems)
-    return 8 * table_words(K) + ((4 * n + 16 + 15) // 16) * 16
+    return _fixed_table_bytes(K) + ((4 * n + 16 + 15) // 16) * 16
 
 
 def use_fixed_frame(n, chunk_elems):
@@ -282,8 +286,9 @@ def pack_fixed(comp):
     for i, f in enumerate((comp.chunk_min, comp.chunk_medium, comp.chunk_type, comp.chunk_crc)):
         if f is not None:
             side[i * K:(i + 1) * K] = f[:K].view(torch.int32)
-    cap = buf.numel() - 8 * tw
-    buf[8 * tw:] = comp.stream[:cap]
+    tb = _fixed_table_bytes(K)
+    cap = min(buf.numel() - tb, comp.stream.numel())
+    buf[tb:tb + cap] = comp.stream[:cap]
     return buf
 
 
@@ -298,7 +303,7 @@ def unpack_fixed(buf, n, chunk_elems, ct, abs_error_bound, flags, compressed_cls
     side = t[HEADER_WORDS + K + 1:].view(torch.int32)
     per_chunk_mask = ct in (7, 9) and not (flags & 2)
     has_crc = bool(flags & 4) or ct in (8, 9)
-    return compressed_cls(ct, n, chunk_elems, abs_error_bound, flags, fixed_type, fixed_mask17, buf[8 * tw:], offs,
+    return compressed_cls(ct, n, chunk_elems, abs_error_bound, flags, fixed_type, fixed_mask17, buf[_fixed_table_bytes(K):], offs,
                           side[0:K].view(torch.float32) if (flags & 1) else None,
                           side[K:2 * K].view(torch.float32) if per_chunk_mask else None,
                           side[2 * K:3 * K] if per_chunk_mask else None,
@@ -318,3 +323,33 @@ def recv_fixed(n, chunk_elems, src, device, ct, abs_error_bound, flags, compress
     buf = buffer if buffer is not None else torch.empty(fixed_frame_bytes(n, chunk_elems), dtype=torch.uint8, device=device)
     dist.recv(buf, src, group=group)
     return unpack_fixed(buf, n, chunk_elems, ct, abs_error_bound, flags, compressed_cls)
+
+
+class FrameWorkspace:
+    """An api.Workspace whose tensors are views of ONE fixed-capacity frame buffer: dcb_compress writes the chunk table and the
+    stream where the frame wants them, so a hop is `dist.send(ws.frame)` with no packing step at all (pack_fixed costs about
+    ten small device ops).  Same field names as api.Workspace; pass it as `workspace=` to api.compress."""
+
+    def __init__(self, n, chunk_elems, device, ct=5, abs_error_bound=0.01, flags=1):
+        import torch
+        from . import api
+        L = api.lib()
+        self.n, self.chunk_elems, self.device = n, chunk_elems, device
+        K = self.K = L.dcb_num_chunks(n, chunk_elems)
+        tw, tb = table_words(K), _fixed_table_bytes(K)
+        self.frame = torch.zeros(fixed_frame_bytes(n, chunk_elems), dtype=torch.uint8, device=device)
+        t = self.frame[:8 * tw].view(torch.int64)
+        eb_bits = int(np.array([abs_error_bound], dtype=np.float64).view(np.int64)[0])
+        t[:HEADER_WORDS] = torch.tensor([MAGIC, ct, n, chunk_elems, eb_bits, flags & 0xFF, 0, 0], dtype=torch.int64).to(device)
+        self.offsets = t[HEADER_WORDS:HEADER_WORDS + K + 1]
+        side = t[HEADER_WORDS + K + 1:].view(torch.int32)
+        self.cmin = side[0:K].view(torch.float32)
+        self.cmed = side[K:2 * K].view(torch.float32)
+        self.ctype = side[2 * K:3 * K]
+        self.ccrc = side[3 * K:4 * K]
+        self.stream = self.frame[tb:]
+        self.capacity = self.stream.numel()
+        assert self.capacity >= L.dcb_max_stream_bytes(n, chunk_elems)
+        self.ws_bytes = L.dcb_workspace_bytes(n, chunk_elems)
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=device)
+        self.status = torch.zeros(1, dtype=torch.int32, device=device)

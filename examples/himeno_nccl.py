@@ -59,6 +59,7 @@ def run(a, ct, rank, world, dev):
     lo = rank - 1 if rank > 0 else None
     hi = rank + 1 if rank < world - 1 else None
     sent = 0
+    mode = getattr(a, "mode", "fixed")
     gosa = torch.zeros(1, dtype=torch.float64, device=dev)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(); dist.barrier()
@@ -67,8 +68,11 @@ def run(a, ct, rank, world, dev):
         g = blk.sweep()
         if ct == 0:
             sent += halo.exchange_axis_raw(blk.p, 3, m, m, m, lo, hi)
-        else:
+        elif mode == "two_round":                       # the reference's message shape: sizes first, then the streams
             sent += halo.exchange_axis(blk.p, 3, m, m, m, lo, hi, ct=ct, eb=a.eb)
+        else:                                           # one fixed-capacity frame per face, no host round trip
+            sent += halo.exchange_axis_fixed(blk.p, 3, m, m, m, lo, hi, ct=ct, eb=a.eb,
+                                             chunk_elems=4096 if mode == "fixed_chunked" else 0)
         gosa.copy_(g)
         dist.all_reduce(gosa)
     ev1.record()
@@ -109,13 +113,16 @@ def main():
     ap.add_argument("--eb", type=float, default=1e-4)
     ap.add_argument("--nn", type=int, default=50)
     ap.add_argument("--check", action="store_true")
+    ap.add_argument("--mode", default="fixed", choices=("fixed", "fixed_chunked", "two_round"),
+                    help="halo frames: one fixed-capacity message per face (a face = ONE reference call, or chunks of 4096 values), "
+                         "or the reference's two rounds (sizes, then streams)")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     m = a.size
-    run(argparse.Namespace(size=m, eb=a.eb, nn=2), a.ct, rank, world, dev)             # warm-up (NCCL channels, allocator)
+    run(argparse.Namespace(size=m, eb=a.eb, nn=2, mode=a.mode), a.ct, rank, world, dev)   # warm-up (NCCL channels, allocator)
     blk, gosa, sent, ms = run(a, a.ct, rank, world, dev)
     ok, note = True, ""
     if a.check:

@@ -87,7 +87,8 @@ int dcb_compress_static(int ct, const float* d_in, uint64_t n, uint64_t chunk_el
                         void* cuda_stream);
 
 /* Mirror of dcb_compress: decodes exactly n values (chunk c holds min(chunk_elems, n - c*chunk_elems)).
- * d_stream must be readable up to the next multiple of 4 bytes past d_chunk_offsets[K].
+ * d_stream must be readable up to the next multiple of 16 bytes past d_chunk_offsets[K] (the decoder fetches 16-byte blocks;
+ * a stream of dcb_max_stream_bytes capacity always is).
  * d_status (device int32, may be NULL) receives DCB_OK / DCB_EFORMAT. */
 int dcb_decompress(int ct, const uint8_t* d_stream, const uint64_t* d_chunk_offsets, uint64_t n,
                    uint64_t chunk_elems, double abs_error_bound, uint32_t flags, int fixed_type,
@@ -186,6 +187,11 @@ int dcb_himeno_jacobi(const float* d_p, const float* d_a, const float* d_b, cons
                       float omega, double* d_gosa, void* cuda_stream);
 int dcb_himeno_copy_interior(float* d_p, const float* d_wrk2, int MI, int MJ, int MK, int imax, int jmax, int kmax,
                              void* cuda_stream);
+
+/* Frees the CALLING THREAD's cached device buffers, pinned staging and stream of the host-pointer layer (dcb_*_host and the
+ * reference's symbols of dataCompression_b200.h keep them between calls, about 12-16 bytes per element).  They are also freed
+ * when the thread exits. */
+int dcb_host_release(void);
 
 /* ---- host-pointer convenience (what the legacy symbols and the end-to-end bench call) ----------------
  * Pinned staging + H2D + kernels + D2H inside.  h_stream needs dcb_max_stream_bytes(); tables need K(+1). */

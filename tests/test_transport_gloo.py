@@ -114,6 +114,33 @@ def _worker(rank, world, port, q):
                                                    chunk_min=got.chunk_min.numpy(), chunk_medium=got.chunk_medium.numpy(),
                                                    chunk_type=got.chunk_type.numpy()), n, chunk, eb)
             assert np.array_equal(dec.view(np.uint32), ol.o_decompress_chunked(ct, wenc, n, chunk, eb).view(np.uint32))
+        # ---- the same hop as ONE fixed-capacity message (no length read back on the host) ---------------------------------
+        for ct in (5, 7, 8):
+            comp, enc = oracle_compressed(x, ct, chunk, eb)
+            flags = 1 | (4 if ct == 8 else 0)
+            comp.flags = flags
+            assert tr.use_fixed_frame(n, chunk)
+            if rank == 0:
+                tr.send_fixed(comp, peer)
+                got = tr.recv_fixed(n, chunk, peer, dev, ct, eb, flags, HostCompressed)
+            else:
+                got = tr.recv_fixed(n, chunk, peer, dev, ct, eb, flags, HostCompressed)
+                tr.send_fixed(comp, peer)
+            xp = make_field("smooth", n, start=1000 * peer)
+            want, wenc = oracle_compressed(xp, ct, chunk, eb)
+            total = int(got.chunk_offsets[-1])
+            assert torch.equal(got.chunk_offsets, want.chunk_offsets)
+            assert np.array_equal(got.stream[:total].numpy(), wenc["stream"])
+            assert torch.equal(got.chunk_min.view(torch.int32), want.chunk_min.view(torch.int32))
+            if ct == 7:
+                assert torch.equal(got.chunk_type, want.chunk_type)
+                assert torch.equal(got.chunk_medium.view(torch.int32), want.chunk_medium.view(torch.int32))
+            else:
+                assert got.chunk_medium is None and got.chunk_type is None
+            if ct == 8:
+                assert torch.equal(got.chunk_crc, want.chunk_crc)
+            else:
+                assert got.chunk_crc is None
         # ---- CT=8 hop with a corrupted first delivery: one resend (impl/pingpong.c:363-410) -----------------------------
         comp, enc = oracle_compressed(x, 8, chunk, eb)
 
