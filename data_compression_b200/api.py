@@ -224,12 +224,16 @@ def compress(x, ct=CT_BITWISE, abs_error_bound=1e-6, chunk_elems=DEFAULT_CHUNK, 
                       ws.ctype if per_chunk_mask else None, ws.ccrc if has_crc else None)
 
 
-def decompress(comp, out=None, status=None):
+def decompress(comp, out=None, status=None, check_status=True):
+    """status: device int32[1] receiving DCB_OK / DCB_EFORMAT (asynchronous; the caller reads it).  Without it the call owns
+    the status word and, unless check_status=False, reads it back (one synchronisation) and raises on a malformed stream -- the
+    condition on which the reference prints "Error leading bit 1" and exits (dataCompression.c:2501-2505)."""
     import torch
     dev = comp.stream.device
     if out is None:
         out = torch.empty(comp.n, dtype=torch.float32, device=dev)
-    if status is None:
+    own_status = status is None
+    if own_status:
         status = torch.zeros(1, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
         rc = lib().dcb_decompress(comp.ct, _ptr(comp.stream), _ptr(comp.chunk_offsets), comp.n, comp.chunk_elems,
@@ -237,6 +241,8 @@ def decompress(comp, out=None, status=None):
                                   _ptr(comp.chunk_min), _ptr(comp.chunk_medium), _ptr(comp.chunk_type), _ptr(out),
                                   _ptr(status), _cur_stream(dev))
     check(rc, "dcb_decompress")
+    if own_status and check_status and int(status.item()) != 0:
+        raise DcbError("dcb_decompress: %s" % ERRORS.get(int(status.item()), status.item()))
     return out
 
 

@@ -158,12 +158,11 @@ __device__ __forceinline__ void pass1_direct(const EncArgs& a, uint64_t cbase, u
 __device__ __noinline__ void exact_medium(const EncArgs& a, WarpBuf& sm, uint64_t cbase, uint64_t cend, float mn, bool submin,
                                           bool slow, bool cbulk, int lane, float& total_out, float& ymx_out, float& y0_out) {
   const float u24 = 1.0f / 16777216.0f;
-  const int cnt = (int)(cend - cbase);
-  const int nr = (cnt + DCB_WR - 1) / DCB_WR;
+  const uint64_t nr = (cend - cbase + DCB_WR - 1) / DCB_WR;         // 64 bit: dcb_stats_kernel calls this for chunks of any length
   float S = 0.0f, ymx = __uint_as_float(0xff800000u), y0 = 0.0f;
   warp_issue_x(a, cbase, cend, sm.X[0], lane, cbulk || round_is_bulk(a, cbase, cend));
   cp_async_commit();
-  for (int j = 0; j < nr; j++) {
+  for (uint64_t j = 0; j < nr; j++) {
     cp_async_wait<0>();
     __syncwarp();
     if (j + 1 < nr) warp_issue_x(a, cbase + (uint64_t)(j + 1) * DCB_WR, cend, sm.X[(j + 1) & 1], lane,

@@ -3,6 +3,7 @@
 // both when a chunk is one tile).  One block per chunk.
 #pragma once
 #include "dcb_common.cuh"
+#include "dcb_encode_warp.cuh"          // exact_medium: the sequential float32 sum without the n-step dependent chain
 
 struct StatsArgs {
   const float* in;
@@ -56,35 +57,38 @@ __global__ void __launch_bounds__(256) dcb_stats_kernel(const StatsArgs a) {
   }
   if (!a.want_medium) return;
 
+  // max, and whether the chunk leaves the domain of the fast exact sum (a negative value, NaN, Inf, |v| >= 2^127)
   float lmx = __uint_as_float(0xff800000u);
+  bool odd = false;
   for (uint64_t i = tid; i < cn; i += 256) {
     float v = __ldg(x + i);
     if (a.subtract_min) v = __fsub_rn(v, mn);
     lmx = fmaxf(lmx, v);
+    odd = odd || !(fabsf(v) < __uint_as_float(0x7f000000u)) || (f2u(v) >> 31);
   }
   #pragma unroll
   for (int o = 16; o; o >>= 1) lmx = fmaxf(lmx, __shfl_xor_sync(0xffffffffu, lmx, o));
-  __syncthreads();
+  const bool slow = __syncthreads_or(odd);
   if (lane == 0) redf[warp] = lmx;
   __syncthreads();
-  if (tid == 0) {
+  if (warp == 0) {
     float mx = redf[0];
     #pragma unroll
     for (int w = 1; w < 8; w++) mx = fmaxf(mx, redf[w]);
-    // the float32 sum must be taken in index order (total += data[i], :3599): one thread, loads batched for ILP
-    float total = 0.0f;
-    uint64_t i = 0;
-    for (; i + 8 <= cn; i += 8) {
-      float v[8];
-      #pragma unroll
-      for (int q = 0; q < 8; q++) v[q] = __ldg(x + i + q);
-      #pragma unroll
-      for (int q = 0; q < 8; q++) total = __fadd_rn(total, a.subtract_min ? __fsub_rn(v[q], mn) : v[q]);
+    // The float32 sum must be the one taken in index order (total += data[i], :3599).  r1 had one thread add the n values
+    // (3.2 ms for the 131,072-float pingpong array); the warp encoder's transducer sum (dcb_encode_warp.cuh, exact_medium:
+    // lanes whose 16 values keep the running sum inside one binade compose exactly) gives the same bits a warp at a time.
+    __shared__ WarpBuf wb;
+    EncArgs ea;
+    ea.in = a.in; ea.n = a.n;
+    ea.flags = ((reinterpret_cast<uintptr_t>(a.in) & 15) == 0) ? DCB_ENC_IN_ALIGNED : 0u;
+    float total, ymx, y0;
+    exact_medium(ea, wb, lo, lo + cn, mn, a.subtract_min != 0, slow, false, lane, total, ymx, y0);
+    if (lane == 0) {
+      float first = __ldg(x);
+      if (a.subtract_min) first = __fsub_rn(first, mn);
+      a.cmed[c] = __fdiv_rn(total, (float)(int)cn);
+      a.ctype[c] = (first != first) ? 0 : type_from_max(mx);
     }
-    for (; i < cn; i++) { const float v = __ldg(x + i); total = __fadd_rn(total, a.subtract_min ? __fsub_rn(v, mn) : v); }
-    float first = __ldg(x);
-    if (a.subtract_min) first = __fsub_rn(first, mn);
-    a.cmed[c] = __fdiv_rn(total, (float)(int)cn);
-    a.ctype[c] = (first != first) ? 0 : type_from_max(mx);
   }
 }

@@ -134,15 +134,19 @@ def send_compressed(comp, dst, group=None):
     return f
 
 
-def recv_compressed(n, chunk_elems, src, device, compressed_cls, group=None, stream_buffer=None):
-    """Posts the fixed-size table receive, reads total_bytes from it, then receives exactly that many stream bytes."""
+def recv_compressed(n, chunk_elems, src, device, compressed_cls, group=None, stream_buffer=None, f64=False):
+    """Posts the fixed-size table receive, reads total_bytes from it, then receives exactly that many stream bytes.
+    f64: the frame carries an api.CompressedF64 (3K table words instead of 2K, codes of up to 64 bits)."""
     import torch
     import torch.distributed as dist
     K = num_chunks(n, chunk_elems)
-    t = torch.empty(table_words(K), dtype=torch.int64, device=device)
+    t = torch.empty(table_words(K, f64), dtype=torch.int64, device=device)
     dist.recv(t, src, group=group)
+    hdr_n, hdr_chunk = int(t[2].item()), int(t[3].item())
+    if (hdr_n, hdr_chunk) != (n, chunk_elems):
+        raise ValueError("frame is for n=%d chunk=%d, expected n=%d chunk=%d" % (hdr_n, hdr_chunk, n, chunk_elems))
     total = int(t[HEADER_WORDS - 1].item())
-    cap = 4 * n + 16                                            # worst case of the stream (every code <= 32 bits)
+    cap = (8 if f64 else 4) * n + 16                            # worst case of the stream (every code <= 32 / 64 bits)
     if total > cap:
         raise ValueError("frame announces %d bytes for %d values" % (total, n))
     buf = stream_buffer if stream_buffer is not None else torch.zeros(((cap + 15) // 16) * 16, dtype=torch.uint8, device=device)

@@ -88,7 +88,9 @@ int dcb_compress_static(int ct, const float* d_in, uint64_t n, uint64_t chunk_el
 
 /* Mirror of dcb_compress: decodes exactly n values (chunk c holds min(chunk_elems, n - c*chunk_elems)).
  * d_stream must be readable up to the next multiple of 16 bytes past d_chunk_offsets[K] (the decoder fetches 16-byte blocks;
- * a stream of dcb_max_stream_bytes capacity always is).
+ * a stream of dcb_max_stream_bytes capacity always is).  The chunk offsets are TRUSTED: they must be monotonic and inside the
+ * stream buffer (the entry point does not know the buffer's capacity); a caller that receives them over an unprotected link
+ * checks them first (transport.recv_compressed does, against n).
  * d_status (device int32, may be NULL) receives DCB_OK / DCB_EFORMAT. */
 int dcb_decompress(int ct, const uint8_t* d_stream, const uint64_t* d_chunk_offsets, uint64_t n,
                    uint64_t chunk_elems, double abs_error_bound, uint32_t flags, int fixed_type,

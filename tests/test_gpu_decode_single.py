@@ -148,3 +148,29 @@ for ct in (5, 6, 7, 11):
         assert r.returncode == 0, r.stderr[-2000:]
         outs.append(r.stdout)
     assert outs[0] == outs[1] and len(outs[0].split()) == 8
+
+
+def test_long_chunk_medium_is_the_sequential_sum(dev):
+    """CT=7 on ONE long chunk: chunk_medium must be med_dataset_float's sequential float32 mean bit for bit (:3593-3620) although
+    a warp computes it (dcb_stats_kernel -> exact_medium), on data that crosses binades, ties, zeros, negatives."""
+    rng = np.random.default_rng(53)
+    n = 150001
+    fields = {
+        "noisy": make_field("noisy", n), "smooth": make_field("smooth", n), "constant": make_field("constant", n),
+        "lognormal": np.exp(rng.normal(0, 4, n)).astype(np.float32),
+        "small_ints": rng.integers(0, 5, n).astype(np.float32),
+        "sparse": np.where(rng.random(n) < 0.05, rng.random(n) * 1e6, 0).astype(np.float32),
+        "growing": (np.arange(n) % 4096).astype(np.float32) ** 2,
+        "tiny_then_big": np.where(np.arange(n) < n // 2, 1e-30, 3.0).astype(np.float32),
+        "negative": (rng.random(n) * 8 - 4).astype(np.float32),
+    }
+    # (no NaN field: a NaN sum becomes the mask, and x86 and the GPU propagate NaN payloads differently -- outside the format)
+    for name, x in fields.items():
+        for sub in (True, False):
+            comp = api.compress(torch.from_numpy(x).to(dev), ct=7, abs_error_bound=0.01, chunk_elems=0, subtract_min=sub)
+            torch.cuda.synchronize()
+            enc = ol.o_compress_chunked(7, x, n, 0.01, subtract_min=sub)
+            got, want = comp.chunk_medium[:1].cpu().numpy(), enc["chunk_medium"]
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)) or (np.isnan(got[0]) and np.isnan(want[0])), (name, sub, got, want)
+            assert int(comp.chunk_type[0].item()) == int(enc["chunk_type"][0]), (name, sub)
+            assert np.array_equal(comp.stream[:comp.total_bytes()].cpu().numpy(), enc["stream"]), (name, sub)
