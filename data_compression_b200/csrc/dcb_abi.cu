@@ -273,6 +273,10 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
     CompactArgs ca;
     ca.slots = a.slots; ca.sizes = a.sizes; ca.gsum = a.gsum; ca.last_tile_bits = a.last_tile_bits; ca.K = K;
     ca.out = d_stream; ca.offsets = d_offsets; ca.last_bits = a.last_bits;
+    // CT=8/9: the CRC of every chunk is computed by the compaction kernel while it copies the chunk (no third pass)
+    static const bool crc_separate = getenv("DCB_CRC_SEPARATE") != nullptr;      // A/B: the r1 stand-alone kernel
+    ca.crc = ((flags & DCB_F_CRC) && !crc_separate) ? d_ccrc : nullptr;
+    if (ca.crc) { int rc_ = ensure_crc_tables(st); if (rc_) return rc_; }
     cudaError_t es;
     if (encoder_choice() == 2) {
       switch (bct) {
@@ -290,7 +294,7 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
       }
     }
     CK(es);
-    if (flags & DCB_F_CRC) {
+    if ((flags & DCB_F_CRC) && !ca.crc) {
       { int rc_ = ensure_crc_tables(st); if (rc_) return rc_; }
       dcb_crc_kernel<<<(unsigned)((K + 3) / 4), 128, 0, st>>>(d_stream, d_offsets, K, d_ccrc);
       CK(cudaGetLastError());

@@ -29,9 +29,14 @@ __device__ __forceinline__ uint32_t crc_shift(uint32_t state, uint64_t nbytes, c
 __device__ uint32_t g_crc_tab[256];
 __device__ uint32_t g_crc_ts[4][256];
 __device__ uint32_t g_crc_c[33];
+//   g_crc_t4[k][i]  (i << 8k) * x^4096 mod P: one Horner step of an accumulator that owns every 128th word (fused CRC of
+//                   dcb_compact_kernel: a lane reads 16-byte units, i.e. four accumulators of stride 128 words)
+//   g_crc_c2[j]     x^(32 j) mod P, j = 0..256
+__device__ uint32_t g_crc_t4[4][256];
+__device__ uint32_t g_crc_c2[257];
 
 __global__ void dcb_crc_init_kernel() {
-  __shared__ uint32_t x1024;
+  __shared__ uint32_t x1024, x4096;
   const int t = threadIdx.x;                       // 256 threads
   if (t == 0) {
     uint32_t p = 0x00800000u;                      // x^8 (x^0 = bit 31)
@@ -40,7 +45,8 @@ __global__ void dcb_crc_init_kernel() {
     uint32_t x32 = 0x00800000u;
     for (int k = 0; k < 2; k++) x32 = gf2_mulmod(x32, x32);    // x^32
     uint32_t c = 0x80000000u;                      // x^0
-    for (int j = 0; j <= 32; j++) { g_crc_c[j] = c; c = gf2_mulmod(c, x32); }
+    for (int j = 0; j <= 256; j++) { if (j <= 32) g_crc_c[j] = c; g_crc_c2[j] = c; c = gf2_mulmod(c, x32); }
+    x4096 = gf2_mulmod(gf2_mulmod(x1024, x1024), gf2_mulmod(x1024, x1024));
   }
   __syncthreads();
   uint32_t c = (uint32_t)t;
@@ -48,6 +54,7 @@ __global__ void dcb_crc_init_kernel() {
   for (int k = 0; k < 8; k++) c = (c & 1u) ? (0xEDB88320u ^ (c >> 1)) : (c >> 1);
   g_crc_tab[t] = c;
   for (int k = 0; k < 4; k++) g_crc_ts[k][t] = gf2_mulmod((uint32_t)t << (8 * k), x1024);
+  for (int k = 0; k < 4; k++) g_crc_t4[k][t] = gf2_mulmod((uint32_t)t << (8 * k), x4096);
 }
 
 // One warp per chunk.  The chunk's 32-bit words are read row by row (32 consecutive words = one coalesced 128-byte load);

@@ -17,6 +17,7 @@
 // B = 4n/r; 0.2 GB for the smooth field, most of it L2 hits), which is far less than what the coupling cost.
 #pragma once
 #include "dcb_encode.cuh"
+#include "dcb_crc.cuh"
 
 #define DCB_SLOT_PITCH 16384u      // bytes per scratch slot: 4096 codes of at most 32 bits
 #define DCB_GROUP 64u              // chunks per compaction block
@@ -681,20 +682,43 @@ struct CompactArgs {
   uint8_t* out;
   uint64_t* offsets;                 // [K+1]
   unsigned long long* last_bits;     // bit length of the whole stream before the final byte round-up (legacy `pos`)
+  uint32_t* crc;                     // [K] or NULL: do_crc32 of every chunk's stream, computed on the bytes as they are copied
+};
+
+struct CrcTabs {                     // shared-memory copies of the tables of dcb_crc.cuh
+  uint32_t tab[256];
+  uint32_t t4[4][256];
+  uint32_t c2[257];
 };
 
 __device__ __forceinline__ uint4 ldg_u4(const uint8_t* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 
-// one warp moves one chunk: n bytes from the 16-byte aligned slot S to the byte address D
-__device__ __forceinline__ void warp_copy_chunk(const uint8_t* __restrict__ S, uint8_t* __restrict__ D, uint32_t n, int lane) {
+// one warp moves one chunk: n bytes from the 16-byte aligned slot S to the byte address D.
+// CRC = true: do_crc32 (dataCompression.c:5524) of the chunk rides on the copy's own loads (r1 ran dcb_crc_kernel over the
+// finished stream: a third pass over B bytes, 0.07-0.24 ms).  The slot is 16-byte aligned and starts the chunk, so source unit
+// j = chunk bytes [16 j, 16 j + 16); lane L loads units L, L + 32, ..: four Horner accumulators of stride 128 words,
+// U_k <- U_k * x^4096 + w_k (four table lookups per word); at the end a lane folds its four (three times x^32 through the
+// byte table), weighs the result with x^(32 (R - i_last)) (one bit-serial multiply) and the warp XORs; the <= 31 bytes behind
+// the last unit it loaded go through the byte table.  Returns the CRC (warp uniform).
+template <bool CRC>
+__device__ __forceinline__ uint32_t warp_copy_chunk(const uint8_t* __restrict__ S, uint8_t* __restrict__ D, uint32_t n, int lane,
+                                                    const CrcTabs* __restrict__ T) {
   const uint32_t a = (uint32_t)(reinterpret_cast<uintptr_t>(D) & 15u);
   const uint32_t head = min(n, (16u - a) & 15u);
   if ((uint32_t)lane < head) D[lane] = S[lane];
   const uint32_t nb = (n - head) >> 4;                   // whole 16-byte units of the destination
   const uint32_t q = head >> 2, b8 = (head & 3u) * 8u;   // warp-uniform source misalignment
   uint4* Dv = reinterpret_cast<uint4*>(D + head);
+  uint32_t U0 = 0u, U1 = 0u, U2 = 0u, U3 = 0u;
   for (uint32_t j = (uint32_t)lane; j < nb; j += 32u) {
     const uint4 A = ldg_u4(S + 16u * j);
+    if (CRC) {
+      const uint32_t w0 = (j == 0u) ? (A.x ^ 0xFFFFFFFFu) : A.x;      // the initial state enters the first word (CRC is linear)
+      U0 = T->t4[0][U0 & 0xFFu] ^ T->t4[1][(U0 >> 8) & 0xFFu] ^ T->t4[2][(U0 >> 16) & 0xFFu] ^ T->t4[3][U0 >> 24] ^ w0;
+      U1 = T->t4[0][U1 & 0xFFu] ^ T->t4[1][(U1 >> 8) & 0xFFu] ^ T->t4[2][(U1 >> 16) & 0xFFu] ^ T->t4[3][U1 >> 24] ^ A.y;
+      U2 = T->t4[0][U2 & 0xFFu] ^ T->t4[1][(U2 >> 8) & 0xFFu] ^ T->t4[2][(U2 >> 16) & 0xFFu] ^ T->t4[3][U2 >> 24] ^ A.z;
+      U3 = T->t4[0][U3 & 0xFFu] ^ T->t4[1][(U3 >> 8) & 0xFFu] ^ T->t4[2][(U3 >> 16) & 0xFFu] ^ T->t4[3][U3 >> 24] ^ A.w;
+    }
     uint4 r;
     if (head == 0u) {
       r = A;
@@ -715,6 +739,28 @@ __device__ __forceinline__ void warp_copy_chunk(const uint8_t* __restrict__ S, u
   const uint32_t done = head + (nb << 4);
   const uint32_t t = n - done;
   if ((uint32_t)lane < t) D[done + lane] = S[done + lane];
+  if (!CRC) return 0u;
+  uint32_t st = 0xFFFFFFFFu;
+  if (nb) {
+    uint32_t v = 0u;
+    if ((uint32_t)lane < nb) {
+      // V = ((U0 x^32 + U1) x^32 + U2) x^32 + U3; a multiplication by x^32 is four zero bytes through the byte table
+      uint32_t V = U0;
+      #pragma unroll
+      for (int k = 0; k < 3; k++) {
+        #pragma unroll
+        for (int z = 0; z < 4; z++) V = T->tab[V & 0xFFu] ^ (V >> 8);
+        V ^= (k == 0) ? U1 : ((k == 1) ? U2 : U3);
+      }
+      const uint32_t jlast = (uint32_t)lane + 32u * ((nb - 1u - (uint32_t)lane) >> 5);   // the last unit this lane loaded
+      v = gf2_mulmod(V, T->c2[4u * (nb - jlast) - 3u]);          // x^(32 (R - i_last)), R = 4 nb words, i_last = 4 jlast + 3
+    }
+    #pragma unroll
+    for (int o = 16; o; o >>= 1) v ^= __shfl_xor_sync(0xffffffffu, v, o);
+    st = v;
+  }
+  for (uint32_t i = nb << 4; i < n; i++) st = T->tab[(st ^ S[i]) & 0xFFu] ^ (st >> 8);   // < 32 bytes, warp uniform
+  return st ^ 0xFFFFFFFFu;
 }
 
 #define DCB_COMPACT_NT 256
@@ -757,8 +803,24 @@ __global__ void __launch_bounds__(DCB_COMPACT_NT) dcb_compact_kernel(const Compa
   if ((uint32_t)tid < cnt) a.offsets[c0 + tid + 1u] = s_off[tid + 1];
   if (g == 0 && tid == 0) a.offsets[0] = 0ull;
   if (c0 + cnt == a.K && tid == 0 && a.last_bits) *a.last_bits = s_off[cnt - 1u] * 8ull + (unsigned long long)__ldg(a.last_tile_bits);
+  if (a.crc) {
+    __shared__ CrcTabs T;
+    for (int i = tid; i < 256; i += DCB_COMPACT_NT) {
+      T.tab[i] = g_crc_tab[i];
+      #pragma unroll
+      for (int k = 0; k < 4; k++) T.t4[k][i] = g_crc_t4[k][i];
+    }
+    for (int i = tid; i < 257; i += DCB_COMPACT_NT) T.c2[i] = g_crc_c2[i];
+    __syncthreads();
+    for (uint32_t k = (uint32_t)warp; k < cnt; k += DCB_COMPACT_NT / 32) {
+      const uint32_t nbytes = (uint32_t)(s_off[k + 1u] - s_off[k]);
+      const uint32_t crc = warp_copy_chunk<true>(a.slots + (c0 + k) * DCB_SLOT_PITCH, a.out + s_off[k], nbytes, lane, &T);
+      if (lane == 0) a.crc[c0 + k] = crc;
+    }
+    return;
+  }
   for (uint32_t k = (uint32_t)warp; k < cnt; k += DCB_COMPACT_NT / 32) {
     const uint32_t nbytes = (uint32_t)(s_off[k + 1u] - s_off[k]);
-    warp_copy_chunk(a.slots + (c0 + k) * DCB_SLOT_PITCH, a.out + s_off[k], nbytes, lane);
+    warp_copy_chunk<false>(a.slots + (c0 + k) * DCB_SLOT_PITCH, a.out + s_off[k], nbytes, lane, nullptr);
   }
 }
