@@ -5,8 +5,8 @@ import subprocess
 import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 n1 = os.path.join(ROOT, "profiles", "bench", "r2_bench_n1_final.json")
-n2 = os.path.join(ROOT, "profiles", "bench", "r2_bench_n2_final.json")
-args = [sys.executable, os.path.join(ROOT, "tools", "sweep_table.py"), n1] + ([n2] if os.path.exists(n2) else [])
+more = [os.path.join(ROOT, "profiles", "bench", "r2_bench_n%d_final.json" % k) for k in (2, 4, 8)]
+args = [sys.executable, os.path.join(ROOT, "tools", "sweep_table.py"), n1] + [m for m in more if os.path.exists(m)]
 tab = subprocess.run(args, capture_output=True, text=True, check=True).stdout
 p = os.path.join(ROOT, "DESIGN.md")
 s = open(p).read()
