@@ -325,6 +325,43 @@ def run_sweep(a, dev, world, rank, peak, fields):
         ok = bool(status.item() == 0) and oracle_check(api, ol, x, comp, out, ct, eb, chunk)
         rows.append({"ct": ct, "field": field, "n": n, "eb": eb, "chunk": chunk, "B": B, "ok": ok})
         times.append([tc, td])
+    # ---- float64 codecs (the *_double entry points of the k-means / MM / LU callers), 2^(log2n-1) doubles
+    del ws_cache
+    fields.clear()
+    torch.cuda.empty_cache()
+    n64 = 1 << (a.log2n - 1)
+    f64_plan = [] if a.sweep == "quick" else [(5, "smooth"), (7, "smooth"), (5, "noisy")]
+    for ct, field in f64_plan:
+        x = make_field_torch(field, n64, dev, start=rank * n64).double()
+        ws = api.WorkspaceF64(n64, 4096, dev)
+        out = torch.empty(n64, dtype=torch.float64, device=dev)
+        status = torch.zeros(1, dtype=torch.int32, device=dev)
+        for _ in range(2):
+            comp = api.compress_f64(x, ct=ct, abs_error_bound=0.01, chunk_elems=4096, workspace=ws)
+            api.decompress_f64(comp, out=out, status=status)
+        ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(a.sweep_steps)]
+        torch.cuda.synchronize()
+        for i in range(a.sweep_steps):
+            ev[i][0].record()
+            comp = api.compress_f64(x, ct=ct, abs_error_bound=0.01, chunk_elems=4096, workspace=ws)
+            ev[i][1].record()
+            api.decompress_f64(comp, out=out, status=status)
+            ev[i][2].record()
+        torch.cuda.synchronize()
+        tc = float(np.mean([e[0].elapsed_time(e[1]) for e in ev]))
+        td = float(np.mean([e[1].elapsed_time(e[2]) for e in ev]))
+        offs = comp.chunk_offsets.cpu().numpy().astype(np.int64)
+        ok = bool(status.item() == 0)
+        for c in (0, (offs.size - 1) // 2, offs.size - 2):                 # sampled chunks against the float64 oracle
+            xs = x[c * 4096:(c + 1) * 4096].cpu().numpy()
+            enc = ol.o_compress_chunked_f64(ct, xs, 4096, 0.01)
+            ok = ok and np.array_equal(comp.stream[int(offs[c]):int(offs[c + 1])].cpu().numpy(), enc["stream"])
+            dec = ol.o_decompress_chunked_f64(ct, enc, 4096, 4096, 0.01)
+            ok = ok and np.array_equal(out[c * 4096:(c + 1) * 4096].cpu().numpy().view(np.uint64), dec.view(np.uint64))
+        rows.append({"ct": ct, "field": field, "n": n64, "eb": 0.01, "chunk": 4096, "B": float(comp.total_bytes()), "ok": ok,
+                     "elem": 8})
+        times.append([tc, td])
+        del x, ws, out
     tt = torch.tensor(times, dtype=torch.float64, device=dev)
     tb = torch.tensor([r["B"] for r in rows], dtype=torch.float64, device=dev)
     okt = torch.tensor([1.0 if r["ok"] else 0.0 for r in rows], dtype=torch.float64, device=dev)
@@ -336,14 +373,16 @@ def run_sweep(a, dev, world, rank, peak, fields):
     out_rows = []
     for r, (tc, td), Bsum, okv in zip(rows, tt, tb, okt):
         n = r["n"]
+        el = float(r.get("elem", 4))                       # bytes per element: 4 (float32) or 8 (the float64 codecs)
         Bg = Bsum / world                                  # stream bytes per GPU
         out_rows.append({
-            "ct": r["ct"], "field": r["field"], "log2n": round(float(np.log2(n)), 3), "n_per_gpu": n, "eb": r["eb"],
-            "chunk": r["chunk"], "ratio": 4.0 * n / max(Bg, 1.0), "compress_ms": tc, "decompress_ms": td,
-            "input_gbs": 4.0 * n * world / ((tc + td) * 1e-3) / 1e9,
-            "roundtrip_frac_of_hbm": (8.0 * n + 2.0 * Bg) / ((tc + td) * 1e-3) / 1e9 / peak,
-            "compress_frac_of_hbm": (4.0 * n + Bg) / (tc * 1e-3) / 1e9 / peak,
-            "decompress_frac_of_hbm": (4.0 * n + Bg) / (td * 1e-3) / 1e9 / peak,
+            "ct": r["ct"], "field": r["field"], "dtype": "f64" if el == 8 else "f32", "log2n": round(float(np.log2(n)), 3),
+            "n_per_gpu": n, "eb": r["eb"],
+            "chunk": r["chunk"], "ratio": el * n / max(Bg, 1.0), "compress_ms": tc, "decompress_ms": td,
+            "input_gbs": el * n * world / ((tc + td) * 1e-3) / 1e9,
+            "roundtrip_frac_of_hbm": (2 * el * n + 2.0 * Bg) / ((tc + td) * 1e-3) / 1e9 / peak,
+            "compress_frac_of_hbm": (el * n + Bg) / (tc * 1e-3) / 1e9 / peak,
+            "decompress_frac_of_hbm": (el * n + Bg) / (td * 1e-3) / 1e9 / peak,
             "oracle_check": bool(okv > 0.5)})
     return out_rows
 

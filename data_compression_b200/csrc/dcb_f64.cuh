@@ -365,15 +365,21 @@ __global__ void __launch_bounds__(128) dcb_f64_decode_kernel(F64DecArgs a) {
   if (CT == CT_MASK && !(a.flags & DCB_F_FIXED_MASK)) { type = a.ctype[c]; mask20 = a.cmask[c]; }
   const int m_mask = f64_mant_bits((uint64_t)mask20 << 44, a.k.n_eb);
   double b3 = -1.0, b2 = -1.0, b1 = -1.0;
-  uint64_t cached = ~0ull; uint32_t w0 = 0, w1 = 0, w2 = 0;
+  // Only 32,768 lanes decode a 2^27-element array (one per chunk), so every latency is exposed (r2 profile: issue active 25 %,
+  // long-scoreboard + wait stalls, 79 instructions per element).  The reader therefore keeps a sliding window of three stream
+  // words plus the next TWO already requested (a code advances the window by at most two words), the position is a word index
+  // and a bit offset (no 64-bit shifts per element), the history is register renaming unless a value is the -1.0 marker
+  // (:2797-2814, rare: exact update), and values leave in pairs as 16-byte stores.
+  uint64_t wi = pos >> 5;
+  uint32_t o = (uint32_t)(pos & 31ull);
+  #define F64_LDW(IDX) ((IDX) < end_word ? s32[(IDX)] : 0u)
+  uint32_t w0 = __byte_perm(F64_LDW(wi), 0u, 0x0123), w1 = __byte_perm(F64_LDW(wi + 1), 0u, 0x0123),
+           w2 = __byte_perm(F64_LDW(wi + 2), 0u, 0x0123);
+  uint32_t n3 = F64_LDW(wi + 3), n4 = F64_LDW(wi + 4);
+  bool full = false;                                               // all three history slots hold a value
+  const bool vec = ((reinterpret_cast<uintptr_t>(a.out + lo) & 15) == 0);
+  double pend = 0.0;
   for (uint64_t i = 0; i < cn; i++) {
-    const uint64_t wi = pos >> 5; const uint32_t o = (uint32_t)(pos & 31ull);
-    if (wi != cached) {
-      w0 = wi < end_word ? __byte_perm(s32[wi], 0u, 0x0123) : 0u;
-      w1 = wi + 1 < end_word ? __byte_perm(s32[wi + 1], 0u, 0x0123) : 0u;
-      w2 = wi + 2 < end_word ? __byte_perm(s32[wi + 2], 0u, 0x0123) : 0u;
-      cached = wi;
-    }
     const uint64_t w = ((uint64_t)__funnelshift_l(w1, w0, o) << 32) | (uint64_t)__funnelshift_l(w2, w1, o);
     double v; int len;
     if (w >> 63) {
@@ -405,11 +411,35 @@ __global__ void __launch_bounds__(128) dcb_f64_decode_kernel(F64DecArgs a) {
       }
       v = __longlong_as_double((long long)(have >= 64 ? top : (top | (0x8000000000000000ull >> have))));
     }
-    pos += (uint64_t)len;
-    a.out[lo + i] = addmin ? __dadd_rn(v, mn) : v;
+    o += (uint32_t)len;
+    const uint32_t adv = o >> 5;                                   // 0, 1 or 2 words
+    o &= 31u;
+    if (adv) {
+      wi += adv;
+      if (adv == 1u) {
+        w0 = w1; w1 = w2; w2 = __byte_perm(n3, 0u, 0x0123);
+        n3 = n4; n4 = F64_LDW(wi + 4);
+      } else {
+        w0 = w2; w1 = __byte_perm(n3, 0u, 0x0123); w2 = __byte_perm(n4, 0u, 0x0123);
+        n3 = F64_LDW(wi + 3); n4 = F64_LDW(wi + 4);
+      }
+    }
+    const double r = addmin ? __dadd_rn(v, mn) : v;
+    if (vec) {
+      if (i & 1ull) *reinterpret_cast<double2*>(a.out + lo + i - 1) = make_double2(pend, r);
+      else if (i + 1 == cn) a.out[lo + i] = r;
+      else pend = r;
+    } else {
+      a.out[lo + i] = r;
+    }
     if (CT != CT_NP) {
-      if (b3 == -1.0) b3 = v; else if (b2 == -1.0) b2 = v; else if (b1 == -1.0) b1 = v;
-      else { b3 = b2; b2 = b1; b1 = v; }
+      if (full && v != -1.0) { b3 = b2; b2 = b1; b1 = v; }
+      else {
+        if (b3 == -1.0) b3 = v; else if (b2 == -1.0) b2 = v; else if (b1 == -1.0) b1 = v;
+        else { b3 = b2; b2 = b1; b1 = v; }
+        full = b3 != -1.0 && b2 != -1.0 && b1 != -1.0;
+      }
     }
   }
+  #undef F64_LDW
 }

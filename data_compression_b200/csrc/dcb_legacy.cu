@@ -125,6 +125,9 @@ __global__ void dcb_subtract_kernel(const float* __restrict__ x, const float* __
     y[i] = __fsub_rn(x[i], m);
 }
 
+// every CUDA call of the front-end symbols is checked: a failed copy must not yield a silently wrong min / medium / CRC
+#define LCK(call, what) do { if ((call) != cudaSuccess) die(what, DCB_ECUDA); } while (0)
+
 struct DevBuf {
   void* p = nullptr;
   explicit DevBuf(size_t bytes) { if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) p = nullptr; }
@@ -141,12 +144,13 @@ extern "C" float toSmallDataset_float(float data[], float** data_small, int num)
   DevBuf dx(n * 4), dy(n * 4), dm(16);
   if (!dx.p || !dy.p || !dm.p) die("cudaMalloc", DCB_ECUDA);
   float mn = 0.0f;
-  cudaMemcpy(dx.p, data, n * 4, cudaMemcpyHostToDevice);
+  LCK(cudaMemcpy(dx.p, data, n * 4, cudaMemcpyHostToDevice), "toSmallDataset_float: copy in");
   int rc = dcb_chunk_stats((const float*)dx.p, n, 0, 0, (float*)dm.p, NULL, NULL, NULL);
   if (rc != DCB_OK) die("dcb_chunk_stats", rc);
   dcb_subtract_kernel<<<1184, 256>>>((const float*)dx.p, (const float*)dm.p, (float*)dy.p, n);
-  cudaMemcpy(*data_small, dy.p, n * 4, cudaMemcpyDeviceToHost);
-  if (cudaMemcpy(&mn, dm.p, 4, cudaMemcpyDeviceToHost) != cudaSuccess) die("toSmallDataset_float", DCB_ECUDA);
+  LCK(cudaGetLastError(), "toSmallDataset_float: launch");
+  LCK(cudaMemcpy(*data_small, dy.p, n * 4, cudaMemcpyDeviceToHost), "toSmallDataset_float: copy out");
+  LCK(cudaMemcpy(&mn, dm.p, 4, cudaMemcpyDeviceToHost), "toSmallDataset_float: min");
   return mn;
 }
 
@@ -157,13 +161,13 @@ extern "C" float med_dataset_float(float* data, int num, int* type) {
   const uint64_t n = (uint64_t)num;
   DevBuf dx(n * 4), dm(48);
   if (!dx.p || !dm.p) die("cudaMalloc", DCB_ECUDA);
-  cudaMemcpy(dx.p, data, n * 4, cudaMemcpyHostToDevice);
+  LCK(cudaMemcpy(dx.p, data, n * 4, cudaMemcpyHostToDevice), "med_dataset_float: copy in");
   float* d_min = (float*)dm.p; float* d_med = d_min + 4; int32_t* d_ty = (int32_t*)(d_min + 8);
   int rc = dcb_chunk_medium((const float*)dx.p, n, d_med, d_ty, NULL);
   if (rc != DCB_OK) die("dcb_chunk_medium", rc);
   float med = 0.0f; int32_t ty = 0;
-  cudaMemcpy(&med, d_med, 4, cudaMemcpyDeviceToHost);
-  if (cudaMemcpy(&ty, d_ty, 4, cudaMemcpyDeviceToHost) != cudaSuccess) die("med_dataset_float", DCB_ECUDA);
+  LCK(cudaMemcpy(&med, d_med, 4, cudaMemcpyDeviceToHost), "med_dataset_float: medium");
+  LCK(cudaMemcpy(&ty, d_ty, 4, cudaMemcpyDeviceToHost), "med_dataset_float: type");
   if (ty != 0) *type = ty;                       // max >= 2^127: the reference leaves *type untouched (:3605-3614)
   return med;
 }
@@ -175,8 +179,8 @@ extern "C" uint32_t do_crc32(unsigned char* data_bits, int bytes) {
   DevBuf ds((size_t)bytes + 16), dt(32);
   if (!ds.p || !dt.p) die("cudaMalloc", DCB_ECUDA);
   const uint64_t offs[2] = {0, (uint64_t)bytes};
-  cudaMemcpy(ds.p, data_bits, (size_t)bytes, cudaMemcpyHostToDevice);
-  cudaMemcpy(dt.p, offs, 16, cudaMemcpyHostToDevice);
+  LCK(cudaMemcpy(ds.p, data_bits, (size_t)bytes, cudaMemcpyHostToDevice), "do_crc32: copy in");
+  LCK(cudaMemcpy(dt.p, offs, 16, cudaMemcpyHostToDevice), "do_crc32: offsets");
   uint32_t* d_crc = (uint32_t*)((char*)dt.p + 16);
   int rc = dcb_crc32_chunks((const uint8_t*)ds.p, (const uint64_t*)dt.p, 1, d_crc, NULL);
   if (rc != DCB_OK) die("dcb_crc32_chunks", rc);
@@ -219,13 +223,13 @@ static void legacy_compress_f64(int ct, double* data, int num, unsigned char** d
   if (!dx.p || !ds.p || !doff.p || !dws.p) die("cudaMalloc", DCB_ECUDA);
   uint32_t flags = 0, m20 = 0;
   if (ct == DCB_CT_BITWISE_MASK) { flags |= DCB_F_FIXED_MASK; m20 = mask20_from_chars(mask); }
-  cudaMemcpy(dx.p, data, n * 8, cudaMemcpyHostToDevice);
+  LCK(cudaMemcpy(dx.p, data, n * 8, cudaMemcpyHostToDevice), "legacy symbol: device copy");
   const int rc = dcb_compress_f64(ct, (const double*)dx.p, n, 0, dc_get_abs_error_bound(), flags, type, m20, (uint8_t*)ds.p, cap,
                                   (uint64_t*)doff.p, NULL, NULL, NULL, NULL, NULL, dws.p, wsb, NULL);
   if (rc != DCB_OK) die("dcb_compress_f64", rc);
   uint64_t offs[2] = {0, 0};
   unsigned long long nbits = 0;
-  cudaMemcpy(offs, doff.p, 16, cudaMemcpyDeviceToHost);
+  LCK(cudaMemcpy(offs, doff.p, 16, cudaMemcpyDeviceToHost), "legacy symbol: device copy");
   if (cudaMemcpy(&nbits, dws.p, 8, cudaMemcpyDeviceToHost) != cudaSuccess) die("myCompress_bitwise_double*", DCB_ECUDA);
   unsigned char* tmp = (unsigned char*)malloc((size_t)(offs[1] ? offs[1] : 1));
   if (!tmp) { printf("ERROR: Out of memory\n"); exit(1); }
@@ -245,14 +249,14 @@ static double* legacy_decompress_f64(int ct, unsigned char* data_bits, int bytes
   const uint64_t offs[2] = {0, nb};
   uint32_t flags = 0, m20 = 0;
   if (ct == DCB_CT_BITWISE_MASK) { flags |= DCB_F_FIXED_MASK; m20 = mask20_from_chars(mask); }
-  cudaMemset(ds.p, 0, (size_t)nb + 16);
-  cudaMemcpy(ds.p, data_bits, (size_t)nb, cudaMemcpyHostToDevice);
-  cudaMemcpy(doff.p, offs, 16, cudaMemcpyHostToDevice);
+  LCK(cudaMemset(ds.p, 0, (size_t)nb + 16), "legacy symbol: device copy");
+  LCK(cudaMemcpy(ds.p, data_bits, (size_t)nb, cudaMemcpyHostToDevice), "legacy symbol: device copy");
+  LCK(cudaMemcpy(doff.p, offs, 16, cudaMemcpyHostToDevice), "legacy symbol: device copy");
   const int rc = dcb_decompress_f64(ct, (const uint8_t*)ds.p, (const uint64_t*)doff.p, n, 0, dc_get_abs_error_bound(), flags, type,
                                     m20, NULL, NULL, NULL, (double*)dout.p, (int32_t*)dst.p, NULL);
   if (rc != DCB_OK) die("dcb_decompress_f64", rc);
   int32_t status = 0;
-  cudaMemcpy(&status, dst.p, 4, cudaMemcpyDeviceToHost);
+  LCK(cudaMemcpy(&status, dst.p, 4, cudaMemcpyDeviceToHost), "legacy symbol: device copy");
   if (cudaMemcpy(out, dout.p, n * 8, cudaMemcpyDeviceToHost) != cudaSuccess) die("myDecompress_bitwise_double*", DCB_ECUDA);
   if (status == DCB_EFORMAT) { printf("Error leading bit 1\n"); exit(1); }
   return out;
@@ -302,11 +306,11 @@ extern "C" double toSmallDataset_double(double data[], double** data_small, int 
   DevBuf dx(n * 8), dy(n * 8), dm(16);
   if (!dx.p || !dy.p || !dm.p) die("cudaMalloc", DCB_ECUDA);
   double mn = 0.0;
-  cudaMemcpy(dx.p, data, n * 8, cudaMemcpyHostToDevice);
+  LCK(cudaMemcpy(dx.p, data, n * 8, cudaMemcpyHostToDevice), "legacy symbol: device copy");
   int rc = dcb_chunk_stats_f64((const double*)dx.p, n, 0, 1, 0, (double*)dm.p, NULL, NULL, NULL, NULL);
   if (rc != DCB_OK) die("dcb_chunk_stats_f64", rc);
   dcb_subtract_f64_kernel<<<1184, 256>>>((const double*)dx.p, (const double*)dm.p, (double*)dy.p, n);
-  cudaMemcpy(*data_small, dy.p, n * 8, cudaMemcpyDeviceToHost);
+  LCK(cudaMemcpy(*data_small, dy.p, n * 8, cudaMemcpyDeviceToHost), "legacy symbol: device copy");
   if (cudaMemcpy(&mn, dm.p, 8, cudaMemcpyDeviceToHost) != cudaSuccess) die("toSmallDataset_double", DCB_ECUDA);
   return mn;
 }
@@ -318,12 +322,12 @@ extern "C" double med_dataset_double(double* data, int num, int* type) {
   const uint64_t n = (uint64_t)num;
   DevBuf dx(n * 8), dm(64);
   if (!dx.p || !dm.p) die("cudaMalloc", DCB_ECUDA);
-  cudaMemcpy(dx.p, data, n * 8, cudaMemcpyHostToDevice);
+  LCK(cudaMemcpy(dx.p, data, n * 8, cudaMemcpyHostToDevice), "legacy symbol: device copy");
   double* d_med = (double*)dm.p; uint32_t* d_mask = (uint32_t*)((char*)dm.p + 16); int32_t* d_ty = (int32_t*)((char*)dm.p + 32);
   int rc = dcb_chunk_stats_f64((const double*)dx.p, n, 0, 0, 1, NULL, d_mask, d_ty, d_med, NULL);
   if (rc != DCB_OK) die("dcb_chunk_stats_f64", rc);
   double med = 0.0; int32_t ty = 0;
-  cudaMemcpy(&med, d_med, 8, cudaMemcpyDeviceToHost);
+  LCK(cudaMemcpy(&med, d_med, 8, cudaMemcpyDeviceToHost), "legacy symbol: device copy");
   if (cudaMemcpy(&ty, d_ty, 4, cudaMemcpyDeviceToHost) != cudaSuccess) die("med_dataset_double", DCB_ECUDA);
   if (ty != 0) *type = ty;
   return med;
@@ -387,18 +391,18 @@ static uint32_t hamming_device(unsigned char* bits, int bytes, uint32_t check_in
   uint32_t check = check_in; int32_t et = 0;
   if (cudaMalloc(&d_b, (size_t)bytes) != cudaSuccess || cudaMalloc(&d_c, 8) != cudaSuccess || cudaMalloc(&d_e, 8) != cudaSuccess)
     die("hamming: cudaMalloc", DCB_ECUDA);
-  cudaMemcpy(d_b, bits, (size_t)bytes, cudaMemcpyHostToDevice);
-  cudaMemcpy(d_c, &check, 4, cudaMemcpyHostToDevice);
+  LCK(cudaMemcpy(d_b, bits, (size_t)bytes, cudaMemcpyHostToDevice), "legacy symbol: device copy");
+  LCK(cudaMemcpy(d_c, &check, 4, cudaMemcpyHostToDevice), "legacy symbol: device copy");
   const int rc = decode ? dcb_hamming_decode(d_b, (uint64_t)bytes, (uint32_t)bytes, d_c, d_e, nullptr)
                         : dcb_hamming_encode(d_b, (uint64_t)bytes, (uint32_t)bytes, d_c, nullptr, nullptr);
   if (rc) die(decode ? "hamming_decode" : "hamming_encode", rc);
   if (cudaMemcpy(&check, d_c, 4, cudaMemcpyDeviceToHost) != cudaSuccess) die("hamming: copy back", DCB_ECUDA);
   if (decode) {
-    cudaMemcpy(&et, d_e, 4, cudaMemcpyDeviceToHost);
+    LCK(cudaMemcpy(&et, d_e, 4, cudaMemcpyDeviceToHost), "legacy symbol: device copy");
     if (et == 3) {                                  // a rectified data bit: find it (for the reference's message), take it over
       unsigned char* fixed = (unsigned char*)malloc((size_t)bytes);
       if (!fixed) { printf("ERROR: Out of memory\n"); exit(1); }
-      cudaMemcpy(fixed, d_b, (size_t)bytes, cudaMemcpyDeviceToHost);
+      LCK(cudaMemcpy(fixed, d_b, (size_t)bytes, cudaMemcpyDeviceToHost), "legacy symbol: device copy");
       for (int i = 0; i < bytes; i++)
         if (fixed[i] != bits[i]) {
           const unsigned x = (unsigned)(fixed[i] ^ bits[i]);

@@ -31,7 +31,7 @@ def main():
     out.append("|---|---|---|---|---|---|---|---|---|---|---|---|---|")
     for s in d.get("sweep", []):
         out.append("| %d | %s | %s | %g | %s | %.2f | %.3f | %.3f | %.0f | %.3f | %.3f | %.3f | %s |" % (
-            s["ct"], s["field"], ("%g" % s["log2n"]), s["eb"], s["chunk"] if s["chunk"] else "one call", s["ratio"], s["compress_ms"],
+            s["ct"], s["field"] + (" (float64)" if s.get("dtype") == "f64" else ""), ("%g" % s["log2n"]), s["eb"], s["chunk"] if s["chunk"] else "one call", s["ratio"], s["compress_ms"],
             s["decompress_ms"], s["input_gbs"], s["roundtrip_frac_of_hbm"], s["compress_frac_of_hbm"], s["decompress_frac_of_hbm"],
             "ok" if s["oracle_check"] else "**FAIL**"))
     for path in sys.argv[2:]:
