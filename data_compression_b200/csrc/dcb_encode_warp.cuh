@@ -46,7 +46,41 @@ struct WarpBuf {
   float X[2][32 * DCB_XPITCH];      // classification pass: double-buffered rounds, one 80-byte slot per lane
   float4 P[128];                    // statistics pass of the next chunk: one round, linear
   uint32_t W[DCB_WWORDS];           // packed round
+  unsigned long long mbar[2];       // [0]: mbarrier of the bulk copy into P (16 bytes keep the array of WarpBufs 16-byte aligned)
 };
+
+// ---- TMA bulk copy of one statistics round (2 KB, linear) ----------------------------------------------------------------------
+// The statistics pass reads the NEXT chunk round by round in plain order, so a round is one contiguous, 16-byte aligned 2 KB
+// block: ONE cp.async.bulk (SASS UBLKCP) issued by lane 0 with an mbarrier for completion can replace four LDGSTS per lane
+// (128 per warp and round).  The classification pass keeps cp.async: its 16 consecutive elements per lane sit at an 80-byte
+// pitch (conflict-free 128-bit reads), which a linear bulk copy cannot produce.
+// MEASURED (round 2, 2^28 smooth, one B200, two A/B runs each): SLOWER than the four LDGSTS -- encoder kernel CT=7 0.597 ms
+// against 0.566, CT=5 compress 0.432 against 0.414 (0.588 / 0.426 without the proxy fence): a 2 KB copy per warp and round is
+// too small for the bulk engine's per-copy cost plus an mbarrier wait per round.  So the default build keeps cp.async
+// (DCB_BULK_P = 0, no UBLKCP in the shipped binary); -DDCB_BULK_P=1 builds this path (parity tests pass on it).
+#ifndef DCB_BULK_P
+#define DCB_BULK_P 0
+#endif
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(smem_u32(bar)) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+}
+__device__ __forceinline__ void bulk_load_2k(void* smem_dst, const void* gsrc, unsigned long long* bar) {
+  // the buffer was read by ordinary loads in the previous round: order them before the asynchronous proxy's writes
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], 2048;\n" ::"r"(smem_u32(bar)) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 2048, [%2];\n"
+               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t phase) {
+  uint32_t done;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(smem_u32(bar)), "r"(phase) : "memory");
+  } while (!done);
+}
 
 struct Pass1 {                      // per-lane partial statistics of a chunk
   float mn, mx, s0, s1, ws, n0, n1;
@@ -101,11 +135,16 @@ __device__ __forceinline__ void warp_issue_x(const EncArgs& a, uint64_t e0, uint
   }
 }
 // statistics pass: the same round of the NEXT chunk, linear
-__device__ __forceinline__ void warp_issue_p(const EncArgs& a, uint64_t e0, float4* P, int lane, bool bulk) {
+__device__ __forceinline__ void warp_issue_p(const EncArgs& a, uint64_t e0, float4* P, int lane, bool bulk,
+                                             unsigned long long* bar) {
   if (bulk) {
     const float* g = a.in + e0;
+#if DCB_BULK_P
+    if (lane == 0) bulk_load_2k(P, g, bar);
+#else
     #pragma unroll
     for (int q = 0; q < 4; q++) cp_async16(&P[q * 32 + lane], g + (q * 32 + lane) * 4);
+#endif
   }
 }
 // j = round inside its chunk (weights: 4096 - index of the float4's first element; only used for whole bulk chunks)
@@ -283,6 +322,11 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
   uint32_t* const W = sm.W;
   const uint32_t one = (a.flags >> 31) + 1u;          // 1, but opaque to the compiler (keeps the field updates on IMAD)
 
+#if DCB_BULK_P
+  if (lane == 0) mbar_init(&sm.mbar[0]);
+  __syncwarp();
+#endif
+  uint32_t pphase = 0u;                              // parity of the statistics buffer's mbarrier
   Pass1 acc;
   p1_reset<CT>(acc);
   pass1_direct<CT>(a, (uint64_t)c * DCB_TILE, min((uint64_t)c * DCB_TILE + DCB_TILE, a.n), lane, acc, submin);
@@ -397,7 +441,7 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
     const bool nbulk = has_next && (nend - nbase) == DCB_TILE && (a.flags & DCB_ENC_IN_ALIGNED);   // every round of the next chunk is a bulk round
     if (fold_next) p1_reset<CT>(acc);
     warp_issue_x(a, cbase, cend, sm.X[0], lane, cbulk || round_is_bulk(a, cbase, cend));
-    if (nrn > 0) warp_issue_p(a, nbase, sm.P, lane, nbulk || round_is_bulk(a, nbase, nend));
+    if (nrn > 0) warp_issue_p(a, nbase, sm.P, lane, nbulk || round_is_bulk(a, nbase, nend), &sm.mbar[0]);
     cp_async_commit();
 
     uint32_t* const out32 = reinterpret_cast<uint32_t*>(a.slots + (uint64_t)cw * DCB_SLOT_PITCH);
@@ -407,12 +451,20 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
     for (int j = 0; j < nr; j++) {
       cp_async_wait<0>();
       __syncwarp();
-      if (j < nrn) warp_consume_p<CT>(a, nbase + (uint64_t)j * DCB_WR, nend, sm.P, lane, acc, submin,
-                                      nbulk || round_is_bulk(a, nbase + (uint64_t)j * DCB_WR, nend), j);
+      if (j < nrn) {
+        const bool pb = nbulk || round_is_bulk(a, nbase + (uint64_t)j * DCB_WR, nend);
+#if DCB_BULK_P
+        if (pb) { mbar_wait(&sm.mbar[0], pphase); pphase ^= 1u; }   // the round's 2 KB have landed (complete_tx)
+#endif
+        warp_consume_p<CT>(a, nbase + (uint64_t)j * DCB_WR, nend, sm.P, lane, acc, submin, pb, j);
+#if DCB_BULK_P
+        __syncwarp();                                  // every lane has read P before lane 0 lets the next copy overwrite it
+#endif
+      }
       if (j + 1 < nr) warp_issue_x(a, cbase + (uint64_t)(j + 1) * DCB_WR, cend, sm.X[(j + 1) & 1], lane,
                                    cbulk || round_is_bulk(a, cbase + (uint64_t)(j + 1) * DCB_WR, cend));
       if (j + 1 < nrn) warp_issue_p(a, nbase + (uint64_t)(j + 1) * DCB_WR, sm.P, lane,
-                                    nbulk || round_is_bulk(a, nbase + (uint64_t)(j + 1) * DCB_WR, nend));
+                                    nbulk || round_is_bulk(a, nbase + (uint64_t)(j + 1) * DCB_WR, nend), &sm.mbar[0]);
       cp_async_commit();
 
       const uint64_t my0 = cbase + (uint64_t)j * DCB_WR + (uint64_t)lane * DCB_E;
