@@ -402,6 +402,7 @@ __device__ __forceinline__ void resolve_pending(const EncArgs& a, EncSmem& sm, i
   unsigned long long P = 0ull;
   if (tile > 0u) {
     const long long dbg_t0 = DBG_CLK();
+    (void)dbg_t0;                                       // only read in -DDCB_DEBUG_COUNTERS builds
     while ((w0 >> ST_SHIFT) != ST_INCL) { __nanosleep(20); w0 = status[tile - 1u]; DBG_ADD(2, 1); }
     DBG_ADD(3, DBG_CLK() - dbg_t0);
     P = w0 & ST_VAL_MASK;

@@ -325,8 +325,8 @@ __global__ void __launch_bounds__(DCB_WNT, (CT == CT_MASK ? DCB_WARP_BLOCKS_CT7 
 #if DCB_BULK_P
   if (lane == 0) mbar_init(&sm.mbar[0]);
   __syncwarp();
-#endif
   uint32_t pphase = 0u;                              // parity of the statistics buffer's mbarrier
+#endif
   Pass1 acc;
   p1_reset<CT>(acc);
   pass1_direct<CT>(a, (uint64_t)c * DCB_TILE, min((uint64_t)c * DCB_TILE + DCB_TILE, a.n), lane, acc, submin);
