@@ -272,7 +272,7 @@ extern "C" int dcb_compress(int ct, const float* d_in, uint64_t n, uint64_t chun
     CK(cudaMemsetAsync(d_ws, 0, (size_t)(ws_head_bytes(n) + 4 * ws_groups(K)), st));
     CompactArgs ca;
     ca.slots = a.slots; ca.sizes = a.sizes; ca.gsum = a.gsum; ca.last_tile_bits = a.last_tile_bits; ca.K = K;
-    ca.out = d_stream; ca.offsets = d_offsets; ca.last_bits = a.last_bits;
+    ca.out = d_stream; ca.offsets = d_offsets; ca.last_bits = a.last_bits; ca.pitch = DCB_SLOT_PITCH;
     // CT=8/9: the CRC of every chunk is computed by the compaction kernel while it copies the chunk (no third pass)
     static const bool crc_separate = getenv("DCB_CRC_SEPARATE") != nullptr;      // A/B: the r1 stand-alone kernel
     ca.crc = ((flags & DCB_F_CRC) && !crc_separate) ? d_ccrc : nullptr;
@@ -543,7 +543,20 @@ extern "C" int dcb_scatter_face(float* d_p, int MI, int MJ, int MK, int ijk, int
 
 // ---- float64 codecs -----------------------------------------------------------------------------
 extern "C" uint64_t dcb_max_stream_bytes_f64(uint64_t n, uint64_t chunk) { (void)chunk; return 8 * n + 16; }
-extern "C" uint64_t dcb_workspace_bytes_f64(uint64_t n, uint64_t chunk) { (void)chunk; return 256 + 8 * num_tiles(n); }
+// float64, one chunk == one tile: the fused encoder's scratch = header | gsum[G] | sizes[K] | K slots of 32 KB
+static bool f64_fused_on() {
+  static const bool on = [] { const char* v = getenv("DCB_F64_FUSED"); return !(v && v[0] == '0'); }();
+  return on;
+}
+static uint64_t ws64_slots_at(uint64_t K) { return (256 + 4 * ws_groups(K) + 4 * K + 255) & ~(uint64_t)255; }
+extern "C" uint64_t dcb_workspace_bytes_f64(uint64_t n, uint64_t chunk) {
+  const uint64_t plain = 256 + 8 * num_tiles(n);
+  if (n && chunk_is_tile(n, chunk)) {
+    const uint64_t fused = ws64_slots_at(num_tiles(n)) + num_tiles(n) * (uint64_t)F64_SLOT_PITCH;
+    return fused > plain ? fused : plain;
+  }
+  return plain;
+}
 
 static int f64_setup(int ct, double eb, uint32_t* flags, int* bct, F64Const* k) {
   *bct = base_ct(ct, flags);
@@ -587,6 +600,36 @@ extern "C" int dcb_compress_f64(int ct, const double* d_in, uint64_t n, uint64_t
   a.tile_bits = (unsigned long long*)((char*)d_ws + 256);
   a.last_bits = (unsigned long long*)d_ws;
 
+  if (chunk_is_tile(n, chunk) && f64_fused_on()) {
+    // one block per chunk keeps the chunk in shared memory from the first load to the packed image (dcb_f64_fused_kernel);
+    // the chunk table, the final placement and the CRC are the float32 path's compaction kernel
+    char* ws = (char*)d_ws;
+    F64FusedArgs f;
+    f.a = a;
+    f.a.chunk = single ? (uint64_t)F64_TILE : chunk;               // blocks index chunks of one tile
+    f.gsum = (uint32_t*)(ws + 256);
+    f.sizes = f.gsum + ws_groups(K);
+    f.slots = (uint8_t*)(ws + ws64_slots_at(K));
+    f.last_tile_bits = (uint32_t*)(ws + 16);
+    f.want_mask = per_chunk_mask ? 1 : 0;
+    f.cmedium = (per_chunk_mask && (flags & DCB_F_EXACT_MEDIUM)) ? d_cmedium : nullptr;
+    CK(cudaMemsetAsync(d_ws, 0, (size_t)(256 + 4 * ws_groups(K)), st));
+    switch (bct) {
+      case CT_BITWISE: dcb_f64_fused_kernel<CT_BITWISE><<<(unsigned)K, F64_NT, 0, st>>>(f); break;
+      case CT_NP: dcb_f64_fused_kernel<CT_NP><<<(unsigned)K, F64_NT, 0, st>>>(f); break;
+      case CT_MASK: dcb_f64_fused_kernel<CT_MASK><<<(unsigned)K, F64_NT, 0, st>>>(f); break;
+      default: dcb_f64_fused_kernel<CT_OP><<<(unsigned)K, F64_NT, 0, st>>>(f); break;
+    }
+    CK(cudaGetLastError());
+    CompactArgs ca;
+    ca.slots = f.slots; ca.sizes = f.sizes; ca.gsum = f.gsum; ca.last_tile_bits = f.last_tile_bits; ca.K = K;
+    ca.out = d_stream; ca.offsets = d_offsets; ca.last_bits = a.last_bits; ca.pitch = F64_SLOT_PITCH;
+    ca.crc = (flags & DCB_F_CRC) ? d_ccrc : nullptr;
+    if (ca.crc) { int rc_ = ensure_crc_tables(st); if (rc_) return rc_; }
+    dcb_compact_kernel<<<(unsigned)ws_groups(K), DCB_COMPACT_NT, 0, st>>>(ca);
+    CK(cudaGetLastError());
+    return DCB_OK;
+  }
   if ((flags & DCB_F_SUBTRACT_MIN) || per_chunk_mask) {
     F64StatsArgs s;
     s.in = d_in; s.n = n; s.chunk = a.chunk; s.subtract_min = (flags & DCB_F_SUBTRACT_MIN) ? 1 : 0;

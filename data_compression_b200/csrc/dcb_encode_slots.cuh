@@ -683,6 +683,7 @@ struct CompactArgs {
   uint64_t* offsets;                 // [K+1]
   unsigned long long* last_bits;     // bit length of the whole stream before the final byte round-up (legacy `pos`)
   uint32_t* crc;                     // [K] or NULL: do_crc32 of every chunk's stream, computed on the bytes as they are copied
+  uint32_t pitch;                    // bytes per slot: DCB_SLOT_PITCH (float32), 32768 (the float64 codecs' fused encoder)
 };
 
 struct CrcTabs {                     // shared-memory copies of the tables of dcb_crc.cuh
@@ -814,13 +815,13 @@ __global__ void __launch_bounds__(DCB_COMPACT_NT) dcb_compact_kernel(const Compa
     __syncthreads();
     for (uint32_t k = (uint32_t)warp; k < cnt; k += DCB_COMPACT_NT / 32) {
       const uint32_t nbytes = (uint32_t)(s_off[k + 1u] - s_off[k]);
-      const uint32_t crc = warp_copy_chunk<true>(a.slots + (c0 + k) * DCB_SLOT_PITCH, a.out + s_off[k], nbytes, lane, &T);
+      const uint32_t crc = warp_copy_chunk<true>(a.slots + (c0 + k) * (uint64_t)a.pitch, a.out + s_off[k], nbytes, lane, &T);
       if (lane == 0) a.crc[c0 + k] = crc;
     }
     return;
   }
   for (uint32_t k = (uint32_t)warp; k < cnt; k += DCB_COMPACT_NT / 32) {
     const uint32_t nbytes = (uint32_t)(s_off[k + 1u] - s_off[k]);
-    warp_copy_chunk<false>(a.slots + (c0 + k) * DCB_SLOT_PITCH, a.out + s_off[k], nbytes, lane, nullptr);
+    warp_copy_chunk<false>(a.slots + (c0 + k) * (uint64_t)a.pitch, a.out + s_off[k], nbytes, lane, nullptr);
   }
 }
