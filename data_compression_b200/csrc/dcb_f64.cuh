@@ -543,6 +543,51 @@ __global__ void __launch_bounds__(128) dcb_f64_decode_kernel(F64DecArgs a) {
   const bool vec = ((reinterpret_cast<uintptr_t>(a.out + lo) & 15) == 0);
   double pend = 0.0;
   for (uint64_t i = 0; i < cn; i++) {
+    // ---- eight 3-bit codes at once (the float32 decoder's fast round): no parse, the code bits only select among the
+    //      predictors; taken when the history is full, and abandoned (nothing committed) if a value comes out negative,
+    //      which the -1.0 marker is -- the code-by-code path below then handles these codes exactly
+    if (CT != CT_NP) {
+      const uint32_t t32 = __funnelshift_l(w1, w0, o);
+      if (full && !(i & 1ull) && i + 8 <= cn && (t32 & 0x92492400u) == 0x92492400u) {
+        double c1 = b1, c2 = b2, c3 = b3;
+        double t1 = __dmul_rn(3.0, c1), t2 = __dmul_rn(3.0, c2);
+        double x8[8];
+        uint32_t neg = 0u;
+        #pragma unroll
+        for (int e = 0; e < 8; e++) {
+          const double p2 = __dsub_rn(__dadd_rn(c1, c1), c2);          // 2.0 * b1 is exact
+          const double p3 = __dadd_rn(__dsub_rn(t1, t2), c3);
+          const bool bb = (t32 & (0x20000000u >> (3 * e))) != 0u;
+          const bool ba = (t32 & (0x40000000u >> (3 * e))) != 0u;
+          const double x = ba ? (bb ? p3 : p2) : (bb ? c1 : 0.0);
+          x8[e] = x;
+          neg |= (uint32_t)((uint64_t)__double_as_longlong(x) >> 32);
+          c3 = c2; c2 = c1; c1 = x; t2 = t1; t1 = __dmul_rn(3.0, x);
+        }
+        if (!(neg >> 31)) {
+          b1 = c1; b2 = c2; b3 = c3;
+          o += 24u;
+          if (o >> 5) {                                              // at most one word
+            o &= 31u; wi += 1;
+            w0 = w1; w1 = w2; w2 = __byte_perm(n3, 0u, 0x0123);
+            n3 = n4; n4 = F64_LDW(wi + 4);
+          }
+          if (addmin) {
+            #pragma unroll
+            for (int e = 0; e < 8; e++) x8[e] = __dadd_rn(x8[e], mn);
+          }
+          if (vec) {
+            #pragma unroll
+            for (int e = 0; e < 8; e += 2) *reinterpret_cast<double2*>(a.out + lo + i + e) = make_double2(x8[e], x8[e + 1]);
+          } else {
+            #pragma unroll
+            for (int e = 0; e < 8; e++) a.out[lo + i + e] = x8[e];
+          }
+          i += 7;                                                    // (+1 by the loop)
+          continue;
+        }
+      }
+    }
     const uint64_t w = ((uint64_t)__funnelshift_l(w1, w0, o) << 32) | (uint64_t)__funnelshift_l(w2, w1, o);
     double v; int len;
     if (w >> 63) {
