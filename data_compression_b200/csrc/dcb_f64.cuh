@@ -378,20 +378,31 @@ __global__ void __launch_bounds__(F64_NT) dcb_f64_fused_kernel(const F64FusedArg
   // ---- toSmallDataset_double (:3522): first minimum with '<' from data[0] (dcb_f64_stats_kernel's rules) --------------
   double mn = 0.0;
   if (sub) {
-    double bv = __longlong_as_double(0x7FF8000000000000ll); uint64_t bi = ~0ull;
-    for (uint32_t e = 1 + tid; e < cnt; e += F64_NT) { const double v = F64_AT(stage, e); if (f64_min_better(v, e, bv, bi)) { bv = v; bi = e; } }
-    for (int o = 16; o; o >>= 1) {
-      const double ov = __shfl_xor_sync(0xffffffffu, bv, o); const uint64_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (f64_min_better(ov, oi, bv, bi)) { bv = ov; bi = oi; }
-    }
-    if (lane == 0) { sh_v[warp] = bv; sh_i[warp] = bi; }
+    // plain minimum first (fmin ignores NaN: a NaN never replaces, :3524-3530); the reference's "first minimal element wins" only
+    // shows when the minimum is a zero (+0 == -0): then the first zero's sign is looked up
+    double bv = __longlong_as_double(0x7FF8000000000000ll);
+    for (uint32_t e = 1 + tid; e < cnt; e += F64_NT) bv = fmin(bv, F64_AT(stage, e));
+    for (int o = 16; o; o >>= 1) bv = fmin(bv, __shfl_xor_sync(0xffffffffu, bv, o));
+    if (lane == 0) sh_v[warp] = bv;
     __syncthreads();
+    double m1 = sh_v[0];
+    #pragma unroll
+    for (int w = 1; w < F64_NT / 32; w++) m1 = fmin(m1, sh_v[w]);
+    if (m1 == 0.0) {                                      // rare: which zero comes first?
+      unsigned long long fi = ~0ull;
+      for (uint32_t e = 1 + tid; e < cnt; e += F64_NT) if (F64_AT(stage, e) == 0.0) { fi = e; break; }
+      for (int o = 16; o; o >>= 1) fi = min(fi, __shfl_xor_sync(0xffffffffu, fi, o));
+      __syncthreads();
+      if (lane == 0) sh_i[warp] = fi;
+      __syncthreads();
+      fi = sh_i[0];
+      #pragma unroll
+      for (int w = 1; w < F64_NT / 32; w++) fi = min(fi, sh_i[w]);
+      m1 = F64_AT(stage, (uint32_t)fi);
+    }
     if (tid == 0) {
       double m = F64_AT(stage, 0);                        // data[0]; a NaN here stays (every '<' is false)
-      if (m == m) {
-        uint64_t mi = 0;
-        for (int w = 0; w < F64_NT / 32; w++) if (f64_min_better(sh_v[w], sh_i[w], m, mi)) { m = sh_v[w]; mi = sh_i[w]; }
-      }
+      if (m == m && m1 == m1 && m1 < m) m = m1;           // strict '<': an equal value (also -0 == +0) never replaces
       sh_mn = m; a.cmin[c] = m;
     }
     __syncthreads();
@@ -450,7 +461,40 @@ __global__ void __launch_bounds__(F64_NT) dcb_f64_fused_kernel(const F64FusedArg
   uint64_t code[F64_PER]; int len[F64_PER];
   const uint32_t my0 = (uint32_t)tid * F64_PER;
   uint32_t bits = 0;
-  {
+  // CLEAN chunk: every value >= 0 and no NaN -- none can be the -1.0 "empty slot" marker, so the reference's history state
+  // machine (:3204-3222) is "the three values before this one" and is read straight from the staged chunk
+  bool dirty = false;
+  for (uint32_t e = tid; e < cnt; e += F64_NT) dirty = dirty || !(F64_AT(stage, e) >= 0.0);
+  const bool clean = (CT != CT_NP) && !__syncthreads_or(dirty);
+  if (clean) {
+    double b3 = 0.0, b2 = 0.0, b1 = 0.0;
+    if (tid > 0) { b3 = stage[(tid - 1) * F64_PITCH + 13]; b2 = stage[(tid - 1) * F64_PITCH + 14]; b1 = stage[(tid - 1) * F64_PITCH + 15]; }
+    #pragma unroll
+    for (int j = 0; j < F64_PER; j++) {
+      code[j] = 0; len[j] = 0;
+      if (my0 + j < cnt) {
+        const double v = stage[tid * F64_PITCH + j];
+        const uint64_t u = (uint64_t)__double_as_longlong(v);
+        const double p2 = __dsub_rn(__dmul_rn(2.0, b1), b2);
+        const double p3 = __dadd_rn(__dsub_rn(__dmul_rn(3.0, b1), __dmul_rn(3.0, b2)), b3);
+        const double d1 = fabs(__dsub_rn(b1, v)), d2 = fabs(__dsub_rn(p2, v)), d3 = fabs(__dsub_rn(p3, v));
+        double dmin = d1; int sel = 5;
+        if (d2 < dmin) { dmin = d2; sel = 6; }
+        if (d3 < dmin) { dmin = d3; sel = 7; }
+        int c3 = 0;
+        if (fabs(v) < a.k.eb) c3 = 4;
+        else if (my0 + j >= 3u && dmin <= a.k.eb) c3 = sel;            // elements 0..2: the history is not full yet (:3204)
+        uint64_t cd; int ln;
+        if (CT == CT_BITWISE) f64_raw(u, a.k.n_eb, cd, ln);
+        else if (CT == CT_OP) { cd = u; ln = 64; }
+        else f64_mask(u, a.k.n_eb, type, mask20, cd, ln);
+        code[j] = c3 ? (uint64_t)c3 : cd;
+        len[j] = c3 ? 3 : ln;
+        bits += (uint32_t)len[j];
+        b3 = b2; b2 = b1; b1 = v;
+      }
+    }
+  } else {
     double b3 = -1.0, b2 = -1.0, b1 = -1.0;
     if (CT != CT_NP && my0 < cnt) f64_entry_state(a.in, lo, lo + my0, mn, sub, b3, b2, b1);
     #pragma unroll
