@@ -701,7 +701,7 @@ extern "C" int dcb_decompress_f64(int ct, const uint8_t* d_stream, const uint64_
   a.stream = d_stream; a.offsets = d_offsets; a.n = n; a.chunk = single ? n : chunk; a.num_chunks = dcb_num_chunks(n, chunk);
   a.flags = flags & 15u; a.fixed_type = fixed_type; a.fixed_mask20 = fixed_mask20;
   a.cmin = d_cmin; a.cmask = d_cmask; a.ctype = d_ctype; a.out = d_out; a.status = d_status;
-  const unsigned grid = (unsigned)((a.num_chunks + 127) / 128);
+  const unsigned grid = (unsigned)((a.num_chunks + 4 * F64_DEC_LANES - 1) / (4 * F64_DEC_LANES));   // 4 warps per block
   switch (bct) {
     case CT_BITWISE: dcb_f64_decode_kernel<CT_BITWISE><<<grid, 128, 0, st>>>(a); break;
     case CT_NP: dcb_f64_decode_kernel<CT_NP><<<grid, 128, 0, st>>>(a); break;
