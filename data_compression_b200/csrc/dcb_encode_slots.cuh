@@ -73,8 +73,7 @@ __device__ __forceinline__ void classify_pred(uint32_t& fields, uint32_t& miss, 
       "abs.f32 a1, %3;\n\t"
       "abs.f32 a2, %4;\n\t"
       "abs.f32 a3, %5;\n\t"
-      "min.f32 dm, a1, a2;\n\t"
-      "min.f32 dm, dm, a3;\n\t"
+      "min.f32 dm, a1, a2, a3;\n\t"                /* sm_100: one FMNMX3 */
       "setp.gt.f32 pnz, %2, %6;\n\t"
       "setp.le.and.f32 ph|pm, dm, %7, pnz;\n\t"      /* pm = !(dm <= tp) && pnz: one FSETP, two predicates */
       "setp.neu.and.f32 pa, a1, dm, ph;\n\t"
