@@ -393,3 +393,44 @@ def test_fuzz_mixed_fields(seed, dev):
     for ct in CTS:
         eb = float(rng.choice(EBS))
         assert_same_as_oracle(x, ct, eb, 4096, dev, tag="fuzz seed=%d ct=%d eb=%g n=%d" % (seed, ct, eb, x.size))
+
+
+def test_stream_offsets_beyond_4_gib(dev):
+    """Just above BASELINE.json configs[2]'s size on ONE GPU (2^30 + 2^24 elements, 266,240 chunks) with the least compressible
+    input of the sweep (CT=11 on the noisy field at 1e-6: 32 bits per element, the fallback is the float itself): the stream is
+    longer than 2^32 bytes, so the offsets of the last chunks need their upper word.  Offsets monotone and ending at the stream length; chunks sampled on both sides
+    of the 4 GiB line and at the very end bit-exact against the oracle (stream, CRC, decoded floats); nothing flagged."""
+    from data_compression_b200.fields import make_field_torch
+    n, chunk, eb, ct = (1 << 30) + (1 << 24), 4096, 1e-6, 11
+    free, _ = torch.cuda.mem_get_info(dev)
+    if free < 30 * (1 << 30):
+        pytest.skip("needs 30 GiB of free device memory")
+    x = make_field_torch("noisy", n, dev)
+    comp = api.compress(x, ct=ct, abs_error_bound=eb, chunk_elems=chunk, crc=True)
+    K = comp.num_chunks
+    assert K == n // chunk
+    offs = comp.chunk_offsets[:K + 1]
+    total = comp.total_bytes()
+    assert total > (1 << 32) and int(offs[K].item()) == total and int(offs[0].item()) == 0
+    assert bool((offs[1:] > offs[:-1]).all().item())
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    out = api.decompress(comp, status=status)
+    torch.cuda.synchronize()
+    assert status.item() == 0
+    offs_h = offs.cpu().numpy().astype(np.int64)
+    line = int(np.searchsorted(offs_h, 1 << 32))                  # first chunk that ends beyond 4 GiB
+    rng = np.random.default_rng(9)
+    picks = sorted(set([0, line - 2, line - 1, line, line + 1, K - 2, K - 1] + [int(v) for v in rng.integers(line, K, 24)]))
+    for c in picks:
+        xc = x[c * chunk:(c + 1) * chunk].cpu().numpy()
+        enc = ol.o_compress_chunked(ct, xc, chunk, eb, want_crc=True)
+        got = comp.stream[offs_h[c]:offs_h[c + 1]].cpu().numpy()
+        assert np.array_equal(got, enc["stream"]), ("chunk", c)
+        assert int(comp.chunk_crc[c].item()) & 0xFFFFFFFF == int(enc["chunk_crc"][0]), ("crc", c)
+        dec = ol.o_decompress_chunked(ct, enc, chunk, chunk, eb)
+        assert np.array_equal(out[c * chunk:(c + 1) * chunk].cpu().numpy().view(np.uint32), dec.view(np.uint32)), ("decoded", c)
+    # CT=11 stores what it cannot predict in full; (x - min) + min re-rounds, nothing more: one ulp of 10 plus the bound
+    worst = float((out - x).abs_().max().item())
+    assert worst <= 1e-6 + 2 * 9.5367431640625e-07, worst
+    del out, comp, x
+    torch.cuda.empty_cache()
