@@ -387,6 +387,77 @@ def run_sweep(a, dev, world, rank, peak, fields):
     return out_rows
 
 
+# ------------------------------------------------------------------------------------------ row N4 (CT=1, CT=10)
+def n4_records(a, dev, peak):
+    """SURVEY.md 8f row N4, measured (rank 0's GPU): the byte-wise codec CT=1 (myCompress / myDecompress,
+    impl/dataCompression.c:3977 / :3942) chunk by chunk, and the Hamming SECDED pass of CT=10 (hamming_encode / hamming_decode
+    :5742 / :5752 as impl/pingpong.c:296-311, :487-505 call them) over a finished CT=5 stream, blocks of 125,000 bytes.
+    Sampled chunks / blocks are compared with the oracle."""
+    import torch
+    from data_compression_b200 import api
+    from data_compression_b200.fields import make_field_torch
+    import oracle_lib as ol
+    n, chunk, eb, steps = 1 << a.log2n, 4096, 0.01, a.sweep_steps
+    recs = []
+
+    def timed(fn):
+        for _ in range(2):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(steps):
+            r = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps, r
+
+    for field in ("smooth", "noisy"):
+        x = make_field_torch(field, n, dev)
+        enc = api.bytewise_compress(x, eb, chunk)
+        out = torch.empty(n, dtype=torch.float32, device=dev)
+        tc, enc = timed(lambda: api.bytewise_compress(x, eb, chunk, buffers=enc))
+        td, _ = timed(lambda: api.bytewise_decompress(enc, out=out))
+        nf = enc["nfloat"].cpu().numpy().astype(np.int64)
+        nfl = int(nf.sum())
+        B = 4.0 * nfl + 5.0 * (n - nfl)                      # floats + (char, int displacement) per hit, as the reference sends them
+        ok = True
+        for c in (0, nf.size // 2, nf.size - 1):
+            xs = x[c * chunk:(c + 1) * chunk].cpu().numpy()
+            af, ac, ad = ol.o_bytewise_compress(xs, eb)
+            lo = c * chunk
+            ok = ok and int(nf[c]) == af.size
+            ok = ok and np.array_equal(enc["array_float"][lo:lo + af.size].cpu().numpy().view(np.uint32), af.view(np.uint32))
+            ok = ok and np.array_equal(enc["array_char"][lo:lo + ac.size].cpu().numpy(), ac)
+            ok = ok and np.array_equal(enc["displacement"][lo:lo + ad.size].cpu().numpy(), ad)
+            dec = ol.o_bytewise_decompress(af, ac, ad, xs.size)
+            ok = ok and np.array_equal(out[lo:lo + xs.size].cpu().numpy().view(np.uint32), dec.view(np.uint32))
+        recs.append({"what": "bytewise_ct1", "field": field, "n": n, "eb": eb, "chunk": chunk, "ratio": 4.0 * n / B,
+                     "compress_ms": tc, "decompress_ms": td, "input_gbs": 4.0 * n / ((tc + td) * 1e-3) / 1e9,
+                     "compress_frac_of_hbm": (4.0 * n + B) / (tc * 1e-3) / 1e9 / peak,
+                     "decompress_frac_of_hbm": (4.0 * n + B) / (td * 1e-3) / 1e9 / peak, "oracle_check": bool(ok)})
+        del enc, out
+        if field == "noisy":
+            comp = api.compress(x, ct=5, abs_error_bound=eb, chunk_elems=chunk)
+            total, bs = comp.total_bytes(), 125000
+            te, (chk, r) = timed(lambda: api.hamming_encode(comp.stream, total, bs))
+            tdec, et = timed(lambda: api.hamming_decode(comp.stream, total, bs, chk))
+            nb = chk.numel()
+            ok = bool((et == 0).all().item())
+            for b in (0, nb // 2, nb - 1):
+                blk = comp.stream[b * bs:min(total, (b + 1) * bs)].cpu().numpy()
+                orr, oc = ol.o_hamming_encode(blk)
+                got = bytes(ord("0") + ((int(chk[b].item()) >> i) & 1) for i in range(orr + 1))
+                ok = ok and int(r[b].item()) == orr and got == oc
+            recs.append({"what": "hamming_ct10", "stream_bytes": total, "block_bytes": bs, "blocks": nb, "encode_ms": te,
+                         "decode_ms": tdec, "encode_gbs": total / (te * 1e-3) / 1e9, "decode_gbs": total / (tdec * 1e-3) / 1e9,
+                         "encode_frac_of_hbm": total / (te * 1e-3) / 1e9 / peak, "oracle_check": bool(ok)})
+            del comp
+        del x
+        torch.cuda.empty_cache()
+    return recs
+
+
 # ------------------------------------------------------------------------------------------ NCCL sub-records (N >= 2)
 def nccl_records(a, dev, rank, world):
     """Compressed payloads moving between GPUs with NCCL send/recv (BASELINE.json configs[0] and configs[3]): the pingpong hop
@@ -749,6 +820,10 @@ def run_ours(a):
         del out
         sweep = run_sweep(a, dev, world, rank, peak, {(a.field, n): x})
 
+    n4 = None
+    if a.sweep == "full" and rank == 0:
+        n4 = n4_records(a, dev, peak)
+
     nccl = None
     if world > 1 and not a.no_nccl:
         nccl = nccl_records(a, dev, rank, world)
@@ -803,6 +878,8 @@ def run_ours(a):
         line["e2e"] = e2e
     if sweep is not None:
         line["sweep"] = sweep
+    if n4 is not None:
+        line["n4"] = n4
     if nccl is not None:
         line["pingpong"] = nccl["pingpong"]
         line["himeno"] = nccl["himeno"]

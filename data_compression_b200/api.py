@@ -361,26 +361,32 @@ def flip_bits(stream, bit_indices):
         check(lib().dcb_flip_bits(_ptr(stream), _ptr(idx), idx.numel(), _cur_stream(stream.device)), "dcb_flip_bits")
 
 
-def bytewise_compress(x, abs_error_bound=1e-6, chunk_elems=DEFAULT_CHUNK):
+def bytewise_compress(x, abs_error_bound=1e-6, chunk_elems=DEFAULT_CHUNK, buffers=None):
     """myCompress (dataCompression.c:3977) per chunk on the device.  -> dict(array_float, array_char, displacement: fixed-pitch
-    tensors of n entries, chunk c at c*chunk_elems; nfloat[K]; n; chunk_elems; abs_error_bound)"""
+    tensors of n entries, chunk c at c*chunk_elems; nfloat[K]; n; chunk_elems; abs_error_bound).  `buffers`: the dict of an
+    earlier call on an input of the same size and type, whose tensors (and workspace) are written again instead of new ones."""
     import torch
     n = x.numel()
     K = max(num_chunks(n, chunk_elems), 1)
     dev = x.device
     f64 = x.dtype == torch.float64
-    af = torch.zeros(max(n, 1), dtype=x.dtype, device=dev)
-    ac = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
-    ad = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)
-    nf = torch.zeros(K, dtype=torch.int32, device=dev)
     wsb = lib().dcb_bytewise_workspace_bytes(n, chunk_elems)
-    ws = torch.empty(max(wsb, 256), dtype=torch.uint8, device=dev)
+    if buffers is not None:
+        if buffers["n"] != n or buffers["chunk_elems"] != chunk_elems or buffers["array_float"].dtype != x.dtype:
+            raise ValueError("bytewise_compress: buffers of another shape")
+        af, ac, ad, nf, ws = (buffers[k] for k in ("array_float", "array_char", "displacement", "nfloat", "workspace"))
+    else:
+        af = torch.zeros(max(n, 1), dtype=x.dtype, device=dev)
+        ac = torch.zeros(max(n, 1), dtype=torch.uint8, device=dev)
+        ad = torch.zeros(max(n, 1), dtype=torch.int32, device=dev)
+        nf = torch.zeros(K, dtype=torch.int32, device=dev)
+        ws = torch.empty(max(wsb, 256), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
         fn = lib().dcb_bytewise_compress_f64 if f64 else lib().dcb_bytewise_compress
         check(fn(_ptr(x), n, chunk_elems, abs_error_bound, _ptr(af), _ptr(ac), _ptr(ad), _ptr(nf), _ptr(ws), wsb,
                  _cur_stream(dev)), "dcb_bytewise_compress")
     return dict(array_float=af, array_char=ac, displacement=ad, nfloat=nf, n=n, chunk_elems=chunk_elems,
-                abs_error_bound=abs_error_bound)
+                abs_error_bound=abs_error_bound, workspace=ws)
 
 
 def bytewise_decompress(enc, out=None):

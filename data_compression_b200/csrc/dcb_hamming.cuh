@@ -46,12 +46,81 @@ __global__ void __launch_bounds__(DCB_HM_NT) dcb_hamming_kernel(const HmArgs a) 
   const uint32_t head = min(nbytes, (uint32_t)((4u - (uint32_t)(reinterpret_cast<uintptr_t>(p) & 3u)) & 3u));
   const uint32_t nwords = (nbytes - head) >> 2;
   const uint32_t tail0 = head + (nwords << 2);
-  for (uint32_t i = (uint32_t)tid; i < head + (nbytes - tail0); i += DCB_HM_NT) {
+  const bool wordpar = head == 0u && nbytes >= 64u && nbytes < (1u << 26);   // (shift t + 2 stays below 32)                          // the word-parallel pass below covers every byte
+  for (uint32_t i = (uint32_t)tid; !wordpar && i < head + (nbytes - tail0); i += DCB_HM_NT) {
     const uint32_t q = (i < head) ? i : (tail0 + (i - head));
     uint32_t v = (uint32_t)p[q] << 24;                   // data bit 8 q + t is bit 7 - t of byte q (cast_bits_to_char, :5712-5722)
     while (v) { const int t = __clz((int)v); v &= ~(0x80000000u >> t); sx ^= hm_pos(8u * q + (uint32_t)t); n1++; }
   }
   const uint32_t* pw = reinterpret_cast<const uint32_t*>(p + head);
+  if (wordpar) {
+    // Word-parallel pass.  Codeword word q = positions 32q .. 32q + 31; for q >= 2 they lie in one region between check
+    // positions, 2^t <= 32q < 2^(t+1), where position = data bit + t + 2: the word is the data bit string shifted by
+    // sh = t + 2 < 32 bits, one funnel shift of data words q - 1 and q (bit j of a data word = data bit 32w + j, i.e. the
+    // stream's bytes bit-reversed).  The XOR of the positions of its set bits splits into (bit index within the word) -- the
+    // XOR over all words of the words themselves, A, reduced to five parities at the very end -- and q for every word of odd
+    // parity.  Position 2^t itself (bit 0 of word q = 2^(t-5)) holds a check bit, not data: those <= 27 words are corrected
+    // afterwards.  Positions below 64 (data bits 0 .. 56) are visited bit by bit.
+    const uint32_t nbits = 8u * nbytes;
+    const uint32_t rr = (uint32_t)hm_length((long long)nbits);
+    const uint32_t Q = ((nbits + rr) >> 5) + 1u;                            // words 0 .. Q-1 hold every position
+    const uint32_t rem = nbytes & 3u;
+    uint32_t lastw = 0u;                                                    // the ragged last data word, zero filled
+    for (uint32_t k = 0; k < rem; k++) lastw |= (uint32_t)p[tail0 + k] << (8u * k);
+    auto load_u = [&](uint32_t w) -> uint32_t {
+      uint32_t x = __ldg(pw + min(w, nwords - 1u));                          // branch free: the loads of a step issue together
+      x = (w < nwords) ? x : ((w == nwords) ? lastw : 0u);
+      return __brev(__byte_perm(x, 0u, 0x0123));
+    };
+    auto cw_of = [&](uint32_t q, uint32_t ulo, uint32_t uhi) -> uint32_t {   // ulo = data word q-1, uhi = data word q
+      const uint32_t sh = (uint32_t)(31 - __clz((int)q)) + 7u;               // t + 2, t = floor(log2 q) + 5
+      return __funnelshift_r(ulo, uhi, 32u - sh);
+    };
+    uint32_t A = 0u, hx = 0u;
+    // a warp takes 128 consecutive words per step, four loads per lane in flight (one load per step left the pass latency
+    // bound: 1.6 TB/s)
+    for (uint32_t q0 = 2u + 128u * (uint32_t)warp; q0 < Q; q0 += 4u * DCB_HM_NT) {
+      uint32_t uhi[4], ul0 = 0u;
+      #pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const uint32_t q = q0 + 32u * (uint32_t)k + (uint32_t)lane;
+        uhi[k] = load_u(q);                                                  // 0 beyond the data
+      }
+      if (lane == 0) ul0 = load_u(q0 - 1u);
+      #pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const uint32_t q = q0 + 32u * (uint32_t)k + (uint32_t)lane;
+        uint32_t ulo = __shfl_up_sync(0xffffffffu, uhi[k], 1);
+        const uint32_t prev = __shfl_sync(0xffffffffu, uhi[(k + 3) & 3], 31);   // lane 0: the last word of the 32 before
+        if (lane == 0) ulo = k ? prev : ul0;
+        if (q < Q) {
+          const uint32_t cw = cw_of(q, ulo, uhi[k]);
+          const uint32_t pc = (uint32_t)__popc(cw);
+          A ^= cw; n1 += pc;
+          hx ^= q & (0u - (pc & 1u));
+        }
+      }
+    }
+    if (tid < 27) {                                                          // take the check positions 2^t (t = 6 ..) out again
+      const uint32_t q = 1u << (tid + 1);
+      if (q >= 2u && q < Q && (cw_of(q, load_u(q - 1u), load_u(q)) & 1u)) { hx ^= q; n1 -= 1u; }
+    }
+    if (tid == 0) {
+      for (uint32_t d = 0; d < nbits; d++) {
+        const uint32_t ps = hm_pos(d);
+        if (ps >= 64u) break;
+        if ((p[d >> 3] >> (7u - (d & 7u))) & 1u) { sx ^= ps; n1++; }
+      }
+    }
+    #pragma unroll
+    for (int o = 16; o; o >>= 1) { A ^= __shfl_xor_sync(0xffffffffu, A, o); hx ^= __shfl_xor_sync(0xffffffffu, hx, o); }
+    if (lane == 0) {
+      const uint32_t lo5 = ((uint32_t)__popc(A & 0xAAAAAAAAu) & 1u) | (((uint32_t)__popc(A & 0xCCCCCCCCu) & 1u) << 1) |
+                           (((uint32_t)__popc(A & 0xF0F0F0F0u) & 1u) << 2) | (((uint32_t)__popc(A & 0xFF00FF00u) & 1u) << 3) |
+                           (((uint32_t)__popc(A & 0xFFFF0000u) & 1u) << 4);
+      sx ^= (hx << 5) | lo5;
+    }
+  } else
   for (uint32_t w = (uint32_t)tid; w < nwords; w += DCB_HM_NT) {
     uint32_t v = __byte_perm(pw[w], 0u, 0x0123);         // MSB = the first data bit of the word
     const uint32_t d0 = 8u * (head + 4u * w);
