@@ -929,6 +929,10 @@ static uint64_t bw_flags_bytes(uint64_t n) { return (n + 255) & ~(uint64_t)255; 
 extern "C" uint64_t dcb_bytewise_workspace_bytes(uint64_t n, uint64_t chunk) {
   return bw_flags_bytes(n) + 4 * bw_tiles(n) + 4 * dcb_num_chunks(n, chunk) + 256;
 }
+static bool bw_three_pass() {                            // DCB_BW_FUSED=0: the three-pass encoder for every shape (A/B, tests)
+  static const bool v = [] { const char* e = getenv("DCB_BW_FUSED"); return e && e[0] == '0'; }();
+  return v;
+}
 template <typename T>
 static int bytewise_compress_t(const T* d_in, uint64_t n, uint64_t chunk, double eb, T* d_val, uint8_t* d_char, int32_t* d_disp,
                                uint32_t* d_chunk_nval, void* d_ws, uint64_t ws_bytes, void* stream) {
@@ -949,6 +953,12 @@ static int bytewise_compress_t(const T* d_in, uint64_t n, uint64_t chunk, double
   a.tile_hits = (uint32_t*)((char*)d_ws + bw_flags_bytes(n));
   a.chunk_slow = a.tile_hits + bw_tiles(n);
   a.chunk_nfloat = d_chunk_nval; a.af = d_val; a.ac = d_char; a.ad = d_disp;
+  a.tiles_per_chunk = single ? 0u : (uint32_t)min(chunk / DCB_BW_NT, (uint64_t)0xFFFFFFFFu);
+  if (!single && chunk <= 65536 && !bw_three_pass()) {     // short chunks: one kernel, one block per chunk
+    dcb_bw_fused_kernel<T><<<(unsigned)K, DCB_BW_NT, 0, st>>>(a);
+    CK(cudaGetLastError());
+    return DCB_OK;
+  }
   CK(cudaMemsetAsync(a.chunk_slow, 0, 4 * K, st));
   dcb_bw_classify_kernel<T><<<(unsigned)bw_tiles(n), DCB_BW_NT, 0, st>>>(a);
   CK(cudaGetLastError());
