@@ -56,7 +56,7 @@ def parse_args():
     ap.add_argument("--eb", type=float, default=0.01)
     ap.add_argument("--chunk", type=int, default=4096)
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--e2e-threads", type=int, default=2, help="host threads making the blocking host-pointer calls")
+    ap.add_argument("--e2e-threads", type=int, default=4, help="host threads making the blocking host-pointer calls")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--sweep", default="full", choices=("full", "quick", "none"),
                     help="extra workloads measured after the headline and reported under \"sweep\" (BASELINE.json configs 1, 3, 5)")
