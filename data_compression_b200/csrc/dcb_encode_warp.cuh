@@ -187,48 +187,64 @@ __device__ __forceinline__ void pass1_direct(const EncArgs& a, uint64_t cbase, u
 }
 
 // med_dataset_float (:3593-3620), exactly, for the chunks whose mask bits the bound cannot pin (and SLOW chunks): one more
-// pass over the chunk in the classification layout.  While the running sum S stays inside one binade [2^e, 2^(e+1)) it
-// lives on the grid q = 2^(e-23), and S -> fl(S + y) commutes with shifts of S by 2q, so a lane whose 16 values provably
-// keep S inside one binade is a 2-state transducer S_out = S_in + d[parity(S_in / q)], d[0], d[1] from two 16-step chains
-// started at 2^e and 2^e + q -- all lanes in parallel, every d exact.  The binade is pinned by S at the start of the round
-// (exact, carried) plus a warp scan of the lanes' plain sums: the reference's running sum before / after lane L lies within
-// (16 L + 48) 1.02 u of it (16 L + 16 adds of the reference, 10 roundings of ours).  Then S is handed from lane to lane:
-// one exact add per lane, or the 16-step chain for the few lanes that straddle a binade (all lanes of a SLOW chunk).
+// pass over the chunk, 32 consecutive values per lane and step (1024 per step).  While the running sum S stays inside one binade
+// [2^e, 2^(e+1)) it lives on the grid q = 2^(e-23), and S -> fl(S + y) commutes with shifts of S by 2q, so a lane whose 32
+// values provably keep S inside one binade is a 2-state transducer S_out = S_in + d[parity(S_in / q)], d[0], d[1] from two
+// 32-step chains started at 2^e and 2^e + q -- all lanes in parallel, every d exact.  The binade is pinned by S at the start
+// of the step (exact, carried) plus a warp scan of the lanes' plain sums: the reference's running sum before / after lane L
+// lies within (32 L + 80) 1.02 u of it (32 L + 32 adds of the reference, 11 roundings of ours).  Then S is handed from run to
+// run of lanes (see "General step" below), or through the 32 values of a lane that straddles a binade (all lanes of a SLOW
+// chunk).
+// Measured (round 2): one call took 27.9k cycles of its warp with 16 values per lane, eight steps and the input staged through
+// shared memory one step ahead -- a chain of dependent latencies (load, tree, scan, two chains, ballots, butterfly) per step,
+// not an instruction count (a cheaper combine stage changed nothing).  Hence half as many, fatter steps, values straight into
+// registers, and the lines of the step after next requested from L1 (prefetch) while this one is worked on.
+#define DCB_XE 32                    // values per lane and step of the exact pass
 __device__ __noinline__ void exact_medium(const EncArgs& a, WarpBuf& sm, uint64_t cbase, uint64_t cend, float mn, bool submin,
                                           bool slow, bool cbulk, int lane, float& total_out, float& ymx_out, float& y0_out) {
+  (void)sm; (void)cbulk;
   const float u24 = 1.0f / 16777216.0f;
-  const uint64_t nr = (cend - cbase + DCB_WR - 1) / DCB_WR;         // 64 bit: dcb_stats_kernel calls this for chunks of any length
+  constexpr uint64_t XR = 32ull * DCB_XE;                            // values per step
+  const uint64_t nr = (cend - cbase + XR - 1) / XR;                  // 64 bit: dcb_stats_kernel calls this for chunks of any length
+  const bool aligned = (a.flags & DCB_ENC_IN_ALIGNED) != 0;
   float S = 0.0f, ymx = __uint_as_float(0xff800000u), y0 = 0.0f;
-  warp_issue_x(a, cbase, cend, sm.X[0], lane, cbulk || round_is_bulk(a, cbase, cend));
-  cp_async_commit();
+  auto prefetch = [&](uint64_t j) {
+    const uint64_t my0 = cbase + j * XR + (uint64_t)lane * DCB_XE;
+    if (my0 < cend) asm volatile("prefetch.global.L1 [%0];" :: "l"(a.in + my0));
+  };
+  prefetch(0);
+  if (nr > 1) prefetch(1);
   for (uint64_t j = 0; j < nr; j++) {
-    cp_async_wait<0>();
-    __syncwarp();
-    if (j + 1 < nr) warp_issue_x(a, cbase + (uint64_t)(j + 1) * DCB_WR, cend, sm.X[(j + 1) & 1], lane,
-                                 cbulk || round_is_bulk(a, cbase + (uint64_t)(j + 1) * DCB_WR, cend));
-    cp_async_commit();
-    const uint64_t my0 = cbase + (uint64_t)j * DCB_WR + (uint64_t)lane * DCB_E;
-    const int vcnt = (my0 >= cend) ? 0 : (int)min((uint64_t)DCB_E, cend - my0);
-    const float* slot = &sm.X[j & 1][lane * DCB_XPITCH];
-    float y[DCB_E];
-    #pragma unroll
-    for (int q = 0; q < 4; q++) {
-      const float4 v = *reinterpret_cast<const float4*>(slot + 4 * q);
-      y[4 * q] = v.x; y[4 * q + 1] = v.y; y[4 * q + 2] = v.z; y[4 * q + 3] = v.w;
+    if (j + 2 < nr) prefetch(j + 2);
+    const uint64_t e0 = cbase + j * XR;
+    const uint64_t my0 = e0 + (uint64_t)lane * DCB_XE;
+    const int vcnt = (my0 >= cend) ? 0 : (int)min((uint64_t)DCB_XE, cend - my0);
+    float y[DCB_XE];
+    if (aligned && e0 + XR <= cend) {
+      const float4* g = reinterpret_cast<const float4*>(a.in + my0);
+      #pragma unroll
+      for (int q = 0; q < DCB_XE / 4; q++) {
+        const float4 v = __ldg(g + q);
+        y[4 * q] = v.x; y[4 * q + 1] = v.y; y[4 * q + 2] = v.z; y[4 * q + 3] = v.w;
+      }
+    } else {
+      #pragma unroll
+      for (int e = 0; e < DCB_XE; e++) y[e] = (e < vcnt) ? __ldg(a.in + my0 + e) : 0.0f;
     }
     if (submin) {
       #pragma unroll
-      for (int e = 0; e < DCB_E; e++) y[e] = (e < vcnt) ? __fsub_rn(y[e], mn) : 0.0f;   // + 0.0f leaves every sum as it is
+      for (int e = 0; e < DCB_XE; e++) y[e] = (e < vcnt) ? __fsub_rn(y[e], mn) : 0.0f;   // + 0.0f leaves every sum as it is
     }
     if (j == 0) y0 = __shfl_sync(0xffffffffu, y[0], 0);
     float d0 = -1.0f, d1 = -1.0f;                        // < 0: not a transducer
     uint32_t ebits = 0u;
     if (!slow) {
-      const float q0 = __fadd_rn(__fadd_rn(y[0], y[1]), __fadd_rn(y[2], y[3]));
-      const float q1 = __fadd_rn(__fadd_rn(y[4], y[5]), __fadd_rn(y[6], y[7]));
-      const float q2 = __fadd_rn(__fadd_rn(y[8], y[9]), __fadd_rn(y[10], y[11]));
-      const float q3 = __fadd_rn(__fadd_rn(y[12], y[13]), __fadd_rn(y[14], y[15]));
-      const float py = __fadd_rn(__fadd_rn(q0, q1), __fadd_rn(q2, q3));
+      float t8[8];
+      #pragma unroll
+      for (int q = 0; q < 8; q++)
+        t8[q] = __fadd_rn(__fadd_rn(y[4 * q], y[4 * q + 1]), __fadd_rn(y[4 * q + 2], y[4 * q + 3]));
+      const float py = __fadd_rn(__fadd_rn(__fadd_rn(t8[0], t8[1]), __fadd_rn(t8[2], t8[3])),
+                                 __fadd_rn(__fadd_rn(t8[4], t8[5]), __fadd_rn(t8[6], t8[7])));
       float inc = py;
       #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -236,7 +252,7 @@ __device__ __noinline__ void exact_medium(const EncArgs& a, WarpBuf& sm, uint64_
         if (lane >= o) inc = __fadd_rn(inc, t);
       }
       const float before = __fadd_rn(S, __fsub_rn(inc, py)), after = __fadd_rn(S, inc);
-      const float r = (float)(16 * lane + 48) * (1.02f * u24);
+      const float r = (float)(DCB_XE * lane + 80) * (1.02f * u24);
       const float lo = __fmul_rd(before, __fsub_rd(1.0f, r));
       const float hi = __fmul_ru(__fmul_ru(after, __fadd_ru(1.0f, r)), 1.00001f);
       const uint32_t elo = f2u(lo) >> 23, ehi = f2u(hi) >> 23;
@@ -244,22 +260,19 @@ __device__ __noinline__ void exact_medium(const EncArgs& a, WarpBuf& sm, uint64_
         const float r0 = u2f(elo << 23), r1 = u2f((elo << 23) | 1u);
         float c0 = r0, c1 = r1;
         #pragma unroll
-        for (int e = 0; e < DCB_E; e++) { c0 = __fadd_rn(c0, y[e]); c1 = __fadd_rn(c1, y[e]); }
+        for (int e = 0; e < DCB_XE; e++) { c0 = __fadd_rn(c0, y[e]); c1 = __fadd_rn(c1, y[e]); }
         d0 = __fsub_rn(c0, r0); d1 = __fsub_rn(c1, r1);  // exact: both ends lie on the grid of one binade
         ebits = elo;
       }
     } else {
       #pragma unroll
-      for (int e = 0; e < DCB_E; e++) if (e < vcnt) ymx = fmaxf(ymx, y[e]);
+      for (int e = 0; e < DCB_XE; e++) if (e < vcnt) ymx = fmaxf(ymx, y[e]);
     }
-    // Runs of consecutive transducer lanes in the same binade compose (associatively) into one transducer: segmented
-    // warp scan, (E then O)_p = E_p + O_{p ^ parity(E_p / q)}, every sum exact.  Then S walks over the run ends and the
-    // lanes that straddle a binade (their 16 values one by one): one or two stops in most rounds.
     const bool certain = d0 >= 0.0f;
     const unsigned cm = __ballot_sync(0xffffffffu, certain);
-    // The common round: every lane is a transducer of the SAME binade and none depends on the parity of S (no tie in its 16
+    // The common step: every lane is a transducer of the SAME binade and none depends on the parity of S (no tie in its 32
     // additions).  Then S_out = S_in + sum of the d0, and that sum is exact in any order (multiples of the binade's grid below
-    // 2^24 grid steps): one butterfly instead of the segmented scan and the walk.
+    // 2^24 grid steps): one butterfly.
     const uint32_t ebits0 = __shfl_sync(0xffffffffu, ebits, 0);
     if (cm == 0xffffffffu && __all_sync(0xffffffffu, d0 == d1 && ebits == ebits0)) {
       float t = d0;
@@ -268,31 +281,46 @@ __device__ __noinline__ void exact_medium(const EncArgs& a, WarpBuf& sm, uint64_
       S = __fadd_rn(S, t);
       continue;
     }
+    // General step.  A transducer lane maps the parity of S / q to the parity after it: p -> p ^ parity(d_p / q), one of the
+    // four maps of {0, 1} (identity, flip, constant 0, constant 1).  Two ballots hold f(0) and f(1) of every lane, and the
+    // parity that ENTERS lane L of a run is read off them with bit operations: the value of the nearest constant lane before L
+    // (or the run's entry parity), flipped once per flip lane in between.  Every lane then knows its increment, and the run's
+    // total is one butterfly (exact: multiples of q, every partial sum below 2^23 q).  So S visits one stop per run of
+    // same-binade transducer lanes and one per straddling lane (its 32 additions done by every lane on its own values, the
+    // straddler's result broadcast) -- no shuffle scan of pairs, no stop per tie.
+    const float rb = u2f(ebits << 23);
+    const unsigned F0 = __ballot_sync(0xffffffffu, certain && (f2u(__fadd_rn(rb, d0)) & 1u) != 0u);   // f(0) = parity(d0 / q)
+    const unsigned F1 = __ballot_sync(0xffffffffu, certain && (f2u(__fadd_rn(rb, d1)) & 1u) == 0u);   // f(1) = 1 ^ parity(d1 / q)
     const uint32_t eprev = __shfl_up_sync(0xffffffffu, ebits, 1);
     const bool head = certain && (lane == 0 || !((cm >> (lane - 1)) & 1u) || eprev != ebits);
     const unsigned hm = __ballot_sync(0xffffffffu, head);
-    const int rs = 31 - __clz((int)(hm & (0xFFFFFFFFu >> (31 - lane))));
-    const float rb = u2f(ebits << 23);
-    #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const float e0 = __shfl_up_sync(0xffffffffu, d0, o), e1 = __shfl_up_sync(0xffffffffu, d1, o);
-      if (certain && lane - o >= rs) {
-        const bool p0 = (f2u(__fadd_rn(rb, e0)) & 1u) != 0u, p1 = (f2u(__fadd_rn(rb, e1)) & 1u) != 0u;
-        const float n0 = __fadd_rn(e0, p0 ? d1 : d0), n1 = __fadd_rn(e1, p1 ? d0 : d1);
-        d0 = n0; d1 = n1;
-      }
-    }
-    const bool tail = certain && (lane == 31 || ((hm >> (lane + 1)) & 1u) || !((cm >> (lane + 1)) & 1u));
-    unsigned m = __ballot_sync(0xffffffffu, !certain || tail);
-    while (m) {                                          // warp-uniform: S is the same in every lane
+    const unsigned cst = ~(F0 ^ F1), flp = F0 & ~F1;
+    const unsigned lt = (1u << lane) - 1u;
+    unsigned m = hm | ~cm;                                 // stops: heads of transducer runs, and every other lane
+    while (m) {                                            // warp-uniform: S is the same in every lane
       const int k = __ffs((int)m) - 1;
       m &= m - 1u;
       if ((cm >> k) & 1u) {
-        const float k0 = __shfl_sync(0xffffffffu, d0, k), k1 = __shfl_sync(0xffffffffu, d1, k);
-        S = __fadd_rn(S, (f2u(S) & 1u) ? k1 : k0);       // exact
-      } else {
+        const unsigned upto = m ? ((1u << (__ffs((int)m) - 1)) - 1u) : 0xffffffffu;
+        const unsigned seg = upto & ~((1u << k) - 1u);     // lanes k .. next stop - 1
+        const unsigned before = seg & lt;                  // lanes of the run before this one
+        const unsigned cb = cst & before;
+        uint32_t pin;
+        if (cb) {
+          const int jc = 31 - __clz((int)cb);
+          pin = ((F0 >> jc) & 1u) ^ ((uint32_t)__popc(flp & before & ~((2u << jc) - 1u)) & 1u);
+        } else {
+          pin = (f2u(S) & 1u) ^ ((uint32_t)__popc(flp & before) & 1u);
+        }
+        float t = ((seg >> lane) & 1u) ? (pin ? d1 : d0) : 0.0f;
         #pragma unroll
-        for (int e = 0; e < DCB_E; e++) S = __fadd_rn(S, __shfl_sync(0xffffffffu, y[e], k));
+        for (int o = 16; o; o >>= 1) t = __fadd_rn(t, __shfl_xor_sync(0xffffffffu, t, o));
+        S = __fadd_rn(S, t);                               // exact
+      } else {
+        float c = S;
+        #pragma unroll
+        for (int e = 0; e < DCB_XE; e++) c = __fadd_rn(c, y[e]);
+        S = __shfl_sync(0xffffffffu, c, k);
       }
     }
   }

@@ -1,5 +1,5 @@
 import ctypes, torch, sys, time
-sys.path.insert(0,'/root/repo')
+sys.path.insert(0,'.')
 from data_compression_b200 import api
 from data_compression_b200.fields import make_field_torch
 dev=torch.device('cuda:0'); n=1<<28
