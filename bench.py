@@ -330,7 +330,7 @@ def run_sweep(a, dev, world, rank, peak, fields):
     fields.clear()
     torch.cuda.empty_cache()
     n64 = 1 << (a.log2n - 1)
-    f64_plan = [] if a.sweep == "quick" else [(5, "smooth"), (7, "smooth"), (5, "noisy")]
+    f64_plan = [] if a.sweep == "quick" else [(5, "smooth"), (7, "smooth"), (6, "smooth"), (11, "smooth"), (5, "noisy"), (7, "noisy")]
     for ct, field in f64_plan:
         x = make_field_torch(field, n64, dev, start=rank * n64).double()
         ws = api.WorkspaceF64(n64, 4096, dev)

@@ -278,43 +278,67 @@ __global__ void __launch_bounds__(128) dcb_resolve_kernel(const ResolveArgs a) {
     int k = 0;                                                      // known non-marker elements in a row up to here
     if (s != 0) { b3 = out[s - 3]; b2 = out[s - 2]; b1 = out[s - 1]; k = 3; }
     uint64_t j = s;
-    uint4 m = gm[j >> 5], m1 = gm[(j >> 5) + 1], m2 = gm[(j >> 5) + 2];
     bool full = b3 != -1.0f && b2 != -1.0f && b1 != -1.0f;
     for (;;) {
-      if ((j & 31ull) == 0ull && j + 32 <= a.n && full && m.x == 0u) {
-        // 32 predicted codes.  One lane walks a long run alone in its warp and nothing hides a latency, so this is
-        // straight-line code: the kind of an element only predicates its additions (a bit test of the group's masks),
-        // the history is register renaming, and the -1.0f marker is looked for afterwards (it is negative: one OR per value).
-        const float s3 = b3, s2 = b2, s1 = b1;
-        const uint32_t mb = m.y, mc = m.z;
-        float v[32];
-        uint32_t neg = 0u;
-        float t1 = __fmul_rn(3.0f, b1), t2 = __fmul_rn(3.0f, b2);
-        #pragma unroll
-        for (int e = 0; e < 32; e++) {
-          const float w = __fadd_rn(b1, b1);                        // 2*b1 is exact (may overflow: no FMA)
-          const float d = __fsub_rn(t1, t2);
-          float x = b1;                                             // 101
-          if (mb & (1u << e)) x = __fsub_rn(w, b2);                 // 110
-          if (mc & (1u << e)) x = __fadd_rn(d, b3);                 // 111
-          v[e] = x; neg |= f2u(x);
-          b3 = b2; b2 = b1; b1 = x; t2 = t1; t1 = __fmul_rn(3.0f, x);
-        }
-        if (neg >> 31) {                                            // a negative value: maybe the marker -> exact state machine
-          b3 = s3; b2 = s2; b1 = s1;
-          #pragma unroll 1
-          for (int e = 0; e < 32; e++) {
-            const uint32_t op = ((mb >> e) & 1u) ? DS_OP_B : (((mc >> e) & 1u) ? DS_OP_C : DS_OP_A);
-            out[j + e] = ds_step_exact(op, 0.0f, b3, b2, b1);
-          }
-          full = b3 != -1.0f && b2 != -1.0f && b1 != -1.0f;
-        } else {
+      if ((j & 31ull) == 0ull && full) {
+        // Groups of 32 predicted codes, as long as they last.  One lane walks a long run alone in its warp and nothing hides
+        // a latency, so this is straight-line code: the kind of an element only predicates its additions (a bit test of the
+        // group's masks), the history is register renaming, and the -1.0f marker is looked for afterwards (it is negative:
+        // one OR per value, four interleaved accumulators).  (Round-2 profile: the arithmetic runs at the ~15 cycles per
+        // element its dependent chain allows; the rest was the mask load and per-group bookkeeping.)
+        // returns 0: group done, go on; 1: not 32 predicted codes (nothing done); 2: done, but the history lost a slot
+        auto group = [&](const uint4& m) -> int {
+          if (m.x != 0u) return 1;
+          const float s3 = b3, s2 = b2, s1 = b1;
+          const uint32_t mb = m.y, mc = m.z;
+          k = 0;                                                    // no known element in this group
+          float v[4];
+          uint32_t neg[4] = {0u, 0u, 0u, 0u};
+          float t1 = __fmul_rn(3.0f, b1), t2 = __fmul_rn(3.0f, b2);
           #pragma unroll
-          for (int e = 0; e < 32; e += 4) *reinterpret_cast<float4*>(out + j + e) = make_float4(v[e], v[e + 1], v[e + 2], v[e + 3]);
+          for (int e = 0; e < 32; e++) {
+            const float w = __fadd_rn(b1, b1);                      // 2*b1 is exact (may overflow: no FMA)
+            const float d = __fsub_rn(t1, t2);
+            float x = b1;                                           // 101
+            if (mb & (1u << e)) x = __fsub_rn(w, b2);               // 110
+            if (mc & (1u << e)) x = __fadd_rn(d, b3);               // 111
+            v[e & 3] = x; neg[e & 3] |= f2u(x);
+            b3 = b2; b2 = b1; b1 = x; t2 = t1; t1 = __fmul_rn(3.0f, x);
+            // stored as soon as four are there (a redo below rewrites the whole group): no burst of stores, and no wait
+            // for their operands, at the end of the group
+            if ((e & 3) == 3) *reinterpret_cast<float4*>(out + j + e - 3) = make_float4(v[0], v[1], v[2], v[3]);
+          }
+          int r = 0;
+          if (((neg[0] | neg[1]) | (neg[2] | neg[3])) >> 31) {      // a negative value: maybe the marker -> exact state machine
+            b3 = s3; b2 = s2; b1 = s1;
+            #pragma unroll 1
+            for (int e = 0; e < 32; e++) {
+              const uint32_t op = ((mb >> e) & 1u) ? DS_OP_B : (((mc >> e) & 1u) ? DS_OP_C : DS_OP_A);
+              out[j + e] = ds_step_exact(op, 0.0f, b3, b2, b1);
+            }
+            full = b3 != -1.0f && b2 != -1.0f && b1 != -1.0f;
+            if (!full) r = 2;
+          }
+          j += 32;
+          return r;
+        };
+        // the masks of the next group are requested before this group's chain starts, into a variable of their own: two
+        // copies of the group in the loop body, no rotation (a rotation's register moves were scheduled right behind the load
+        // and waited for it: 17-22 % of the kernel's samples)
+        uint64_t g = j >> 5;                                        // gm is padded: g + 1 is always readable
+        uint4 mA = gm[g], mB;                                       // (pinning these loads with volatile asm was slower: 0.985 vs 0.903 ms)
+        while (j + 32 <= a.n) {
+          mB = gm[g + 1];
+          if (group(mA)) break;
+          g++;
+          if (j + 32 > a.n) break;
+          mA = gm[g + 1];
+          if (group(mB)) break;
+          g++;
         }
-        k = 0;
-        j += 32;
-      } else {
+        if (j >= a.n) break;
+      }
+      {
         const uint32_t op = ops[j];
         const bool kno = (op == DS_OP_ZERO || op == DS_OP_KNOWN);
         const float kv = kno ? out[j] : 0.0f;
@@ -325,8 +349,6 @@ __global__ void __launch_bounds__(128) dcb_resolve_kernel(const ResolveArgs a) {
         j++;
         if (j >= a.n || k >= 3) break;                              // element j starts the next run
       }
-      if (j >= a.n) break;
-      if ((j & 31ull) == 0ull) { m = m1; m1 = m2; m2 = gm[(j >> 5) + 2]; }
     }
     // the elements s+1 .. j-1 start no run; continue the ownership scan at j
     if (j >= hi) return;
