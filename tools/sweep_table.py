@@ -34,6 +34,21 @@ def main():
             s["ct"], s["field"] + (" (float64)" if s.get("dtype") == "f64" else ""), ("%g" % s["log2n"]), s["eb"], s["chunk"] if s["chunk"] else "one call", s["ratio"], s["compress_ms"],
             s["decompress_ms"], s["input_gbs"], s["roundtrip_frac_of_hbm"], s["compress_frac_of_hbm"], s["decompress_frac_of_hbm"],
             "ok" if s["oracle_check"] else "**FAIL**"))
+    if d.get("n4"):
+        out.append("")
+        out.append("Row N4 (`n4` of the same line; 2^%d floats, chunk 4096, absErrorBound 0.01; Hamming over the CT=5 stream of the noisy field):" % round(d["sweep"][0]["log2n"]))
+        out.append("")
+        out.append("| kernel | field / size | ratio | compress (encode) ms | decompress (decode) ms | GB/s | / HBM | oracle check |")
+        out.append("|---|---|---|---|---|---|---|---|")
+        for q in d["n4"]:
+            if q["what"] == "bytewise_ct1":
+                out.append("| CT=1 byte-wise (`myCompress` / `myDecompress`) | %s | %.2f | %.3f | %.3f | %.0f of input, round trip | %.2f / %.2f | %s |" % (
+                    q["field"], q["ratio"], q["compress_ms"], q["decompress_ms"], q["input_gbs"], q["compress_frac_of_hbm"],
+                    q["decompress_frac_of_hbm"], "ok" if q["oracle_check"] else "**FAIL**"))
+            else:
+                out.append("| CT=10 Hamming SECDED, blocks of %d bytes | %d-byte stream, %d blocks | | %.3f | %.3f | %.0f / %.0f | %.2f (encode) | %s |" % (
+                    q["block_bytes"], q["stream_bytes"], q["blocks"], q["encode_ms"], q["decode_ms"], q["encode_gbs"], q["decode_gbs"],
+                    q["encode_frac_of_hbm"], "ok" if q["oracle_check"] else "**FAIL**"))
     for path in sys.argv[2:]:
         m = json.load(open(path))
         out.append("")
