@@ -196,7 +196,11 @@ int dcb_himeno_copy_interior(float* d_p, const float* d_wrk2, int MI, int MJ, in
 int dcb_host_release(void);
 
 /* ---- host-pointer convenience (what the legacy symbols and the end-to-end bench call) ----------------
- * Pinned staging + H2D + kernels + D2H inside.  h_stream needs dcb_max_stream_bytes(); tables need K(+1). */
+ * Pinned staging + H2D + kernels + D2H inside.  h_stream needs dcb_max_stream_bytes(); tables need K(+1).
+ * Blocking and thread safe: every calling thread has its own stream and device buffers.  Bulk copies go out in slices of
+ * DCB_COPY_SLICE_MB megabytes (environment, default 128) under a FIFO lock per direction, so that concurrent callers keep
+ * both copy engines busy: measured on one B200 with pinned buffers, one caller 24.9 GB/s of input (compress + decompress),
+ * four callers 43.5 GB/s = 0.95 of what plain concurrent cudaMemcpyAsync in both directions reaches on that box. */
 int dcb_compress_host(int ct, const float* h_in, uint64_t n, uint64_t chunk_elems, double abs_error_bound,
                       uint32_t flags, int fixed_type, uint32_t fixed_mask17,
                       uint8_t* h_stream, uint64_t* h_chunk_offsets, float* h_chunk_min, float* h_chunk_medium,
