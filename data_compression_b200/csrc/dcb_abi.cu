@@ -20,6 +20,7 @@
 #include "dcb_crc.cuh"
 #include "dcb_face.cuh"
 #include "dcb_f64.cuh"
+#include "dcb_decode_single_f64.cuh"
 #include "dcb_hamming.cuh"
 #include "dcb_bytewise.cuh"
 static int ensure_crc_tables(cudaStream_t st);
@@ -701,6 +702,26 @@ extern "C" int dcb_decompress_f64(int ct, const uint8_t* d_stream, const uint64_
   a.stream = d_stream; a.offsets = d_offsets; a.n = n; a.chunk = single ? n : chunk; a.num_chunks = dcb_num_chunks(n, chunk);
   a.flags = flags & 15u; a.fixed_type = fixed_type; a.fixed_mask20 = fixed_mask20;
   a.cmin = d_cmin; a.cmask = d_cmask; a.ctype = d_ctype; a.out = d_out; a.status = d_status;
+  // ONE chunk of more than a tile (the *_double call shape of k-means / MM / LU): codes located and resolved in parallel
+  // inside the chunk (dcb_decode_single_f64.cuh); scratch from the library's stream-ordered pool.  DCB_DECODER=lane: one thread.
+  static const bool lane_only = [] { const char* v = getenv("DCB_DECODER"); return v && !strcmp(v, "lane"); }();
+  if (a.num_chunks == 1 && n > F64_TILE && n < (1ull << 32) && !lane_only) {
+    void* ws = nullptr;
+    cudaMemPool_t pool = nullptr;
+    { int rc_ = scratch_pool(&pool); if (rc_) return rc_; }
+    CK(cudaMallocFromPoolAsync(&ws, (size_t)ds64_workspace_bytes(n), pool, st));
+    cudaError_t e;
+    switch (bct) {
+      case CT_BITWISE: e = ds64_launch<CT_BITWISE>(a, ws, st); break;
+      case CT_NP: e = ds64_launch<CT_NP>(a, ws, st); break;
+      case CT_MASK: e = ds64_launch<CT_MASK>(a, ws, st); break;
+      default: e = ds64_launch<CT_OP>(a, ws, st); break;
+    }
+    cudaError_t ef = cudaFreeAsync(ws, st);
+    CK(e);
+    CK(ef);
+    return DCB_OK;
+  }
   const unsigned grid = (unsigned)((a.num_chunks + 4 * F64_DEC_LANES - 1) / (4 * F64_DEC_LANES));   // 4 warps per block
   switch (bct) {
     case CT_BITWISE: dcb_f64_decode_kernel<CT_BITWISE><<<grid, 128, 0, st>>>(a); break;
