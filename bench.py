@@ -330,20 +330,22 @@ def run_sweep(a, dev, world, rank, peak, fields):
     fields.clear()
     torch.cuda.empty_cache()
     n64 = 1 << (a.log2n - 1)
-    f64_plan = [] if a.sweep == "quick" else [(5, "smooth"), (7, "smooth"), (6, "smooth"), (11, "smooth"), (5, "noisy"), (7, "noisy")]
-    for ct, field in f64_plan:
+    f64_plan = [] if a.sweep == "quick" else [(5, "smooth", n64, 4096), (7, "smooth", n64, 4096), (6, "smooth", n64, 4096),
+                                              (11, "smooth", n64, 4096), (5, "noisy", n64, 4096), (7, "noisy", n64, 4096),
+                                              (5, "smooth", 1 << 20, 0), (5, "noisy", 1 << 20, 0)]   # chunk 0: ONE call (k-means / MM / LU shape)
+    for ct, field, n64, ch64 in f64_plan:
         x = make_field_torch(field, n64, dev, start=rank * n64).double()
-        ws = api.WorkspaceF64(n64, 4096, dev)
+        ws = api.WorkspaceF64(n64, ch64, dev)
         out = torch.empty(n64, dtype=torch.float64, device=dev)
         status = torch.zeros(1, dtype=torch.int32, device=dev)
         for _ in range(2):
-            comp = api.compress_f64(x, ct=ct, abs_error_bound=0.01, chunk_elems=4096, workspace=ws)
+            comp = api.compress_f64(x, ct=ct, abs_error_bound=0.01, chunk_elems=ch64, workspace=ws)
             api.decompress_f64(comp, out=out, status=status)
         ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(a.sweep_steps)]
         torch.cuda.synchronize()
         for i in range(a.sweep_steps):
             ev[i][0].record()
-            comp = api.compress_f64(x, ct=ct, abs_error_bound=0.01, chunk_elems=4096, workspace=ws)
+            comp = api.compress_f64(x, ct=ct, abs_error_bound=0.01, chunk_elems=ch64, workspace=ws)
             ev[i][1].record()
             api.decompress_f64(comp, out=out, status=status)
             ev[i][2].record()
@@ -352,13 +354,19 @@ def run_sweep(a, dev, world, rank, peak, fields):
         td = float(np.mean([e[1].elapsed_time(e[2]) for e in ev]))
         offs = comp.chunk_offsets.cpu().numpy().astype(np.int64)
         ok = bool(status.item() == 0)
-        for c in (0, (offs.size - 1) // 2, offs.size - 2):                 # sampled chunks against the float64 oracle
+        if ch64 == 0:                                                      # one call: the whole array against the oracle
+            xs = x.cpu().numpy()
+            enc = ol.o_compress_chunked_f64(ct, xs, n64, 0.01)
+            ok = ok and np.array_equal(comp.stream[:int(offs[-1])].cpu().numpy(), enc["stream"])
+            dec = ol.o_decompress_chunked_f64(ct, enc, n64, n64, 0.01)
+            ok = ok and np.array_equal(out.cpu().numpy().view(np.uint64), dec.view(np.uint64))
+        for c in (() if ch64 == 0 else (0, (offs.size - 1) // 2, offs.size - 2)):   # sampled chunks against the float64 oracle
             xs = x[c * 4096:(c + 1) * 4096].cpu().numpy()
             enc = ol.o_compress_chunked_f64(ct, xs, 4096, 0.01)
             ok = ok and np.array_equal(comp.stream[int(offs[c]):int(offs[c + 1])].cpu().numpy(), enc["stream"])
             dec = ol.o_decompress_chunked_f64(ct, enc, 4096, 4096, 0.01)
             ok = ok and np.array_equal(out[c * 4096:(c + 1) * 4096].cpu().numpy().view(np.uint64), dec.view(np.uint64))
-        rows.append({"ct": ct, "field": field, "n": n64, "eb": 0.01, "chunk": 4096, "B": float(comp.total_bytes()), "ok": ok,
+        rows.append({"ct": ct, "field": field, "n": n64, "eb": 0.01, "chunk": ch64, "B": float(comp.total_bytes()), "ok": ok,
                      "elem": 8})
         times.append([tc, td])
         del x, ws, out
