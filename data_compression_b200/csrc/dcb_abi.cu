@@ -21,6 +21,7 @@
 #include "dcb_face.cuh"
 #include "dcb_f64.cuh"
 #include "dcb_decode_single_f64.cuh"
+#include "dcb_f64_stats_long.cuh"
 #include "dcb_hamming.cuh"
 #include "dcb_bytewise.cuh"
 static int ensure_crc_tables(cudaStream_t st);
@@ -566,6 +567,26 @@ static int f64_setup(int ct, double eb, uint32_t* flags, int* bct, F64Const* k) 
   return DCB_OK;
 }
 
+// per-chunk statistics of the float64 codecs: one block per chunk, except ONE long chunk (the single-call shape), which is
+// cut into parts (dcb_f64_stats_long.cuh; scratch from the library's stream-ordered pool)
+static int f64_stats_run(const F64StatsArgs& s, uint64_t K, cudaStream_t st) {
+  static const bool one_block = [] { const char* v = getenv("DCB_F64_STATS"); return v && !strcmp(v, "block"); }();
+  if (K == 1 && s.n >= 65536 && !one_block) {
+    void* ws = nullptr;
+    cudaMemPool_t pool = nullptr;
+    { int rc_ = scratch_pool(&pool); if (rc_) return rc_; }
+    CK(cudaMallocFromPoolAsync(&ws, (size_t)f64l_scratch_bytes(), pool, st));
+    cudaError_t e = f64l_launch(s, ws, st);
+    cudaError_t ef = cudaFreeAsync(ws, st);
+    CK(e);
+    CK(ef);
+    return DCB_OK;
+  }
+  dcb_f64_stats_kernel<<<(unsigned)K, F64_NT, 0, st>>>(s);
+  CK(cudaGetLastError());
+  return DCB_OK;
+}
+
 extern "C" int dcb_compress_f64(int ct, const double* d_in, uint64_t n, uint64_t chunk, double eb, uint32_t flags,
                                 int fixed_type, uint32_t fixed_mask20, uint8_t* d_stream, uint64_t capacity,
                                 uint64_t* d_offsets, double* d_cmin, uint32_t* d_cmask, int32_t* d_ctype, double* d_cmedium,
@@ -637,8 +658,7 @@ extern "C" int dcb_compress_f64(int ct, const double* d_in, uint64_t n, uint64_t
     s.want_mask = per_chunk_mask ? 1 : 0;
     s.cmin = d_cmin; s.cmask = d_cmask; s.ctype = d_ctype;
     s.cmedium = (per_chunk_mask && (flags & DCB_F_EXACT_MEDIUM)) ? d_cmedium : nullptr;
-    dcb_f64_stats_kernel<<<(unsigned)K, F64_NT, 0, st>>>(s);
-    CK(cudaGetLastError());
+    { int rc_ = f64_stats_run(s, K, st); if (rc_) return rc_; }
   }
   switch (bct) {
     case CT_BITWISE: dcb_f64_length_kernel<CT_BITWISE><<<a.num_tiles, F64_NT, 0, st>>>(a); break;
@@ -676,9 +696,7 @@ extern "C" int dcb_chunk_stats_f64(const double* d_in, uint64_t n, uint64_t chun
   F64StatsArgs s;
   s.in = d_in; s.n = n; s.chunk = single ? n : chunk; s.subtract_min = subtract_min ? 1 : 0; s.want_mask = want_medium ? 1 : 0;
   s.cmin = d_cmin; s.cmask = d_cmask; s.ctype = d_ctype; s.cmedium = d_cmedium;
-  dcb_f64_stats_kernel<<<(unsigned)dcb_num_chunks(n, chunk), F64_NT, 0, (cudaStream_t)stream>>>(s);
-  CK(cudaGetLastError());
-  return DCB_OK;
+  return f64_stats_run(s, dcb_num_chunks(n, chunk), (cudaStream_t)stream);
 }
 
 extern "C" int dcb_decompress_f64(int ct, const uint8_t* d_stream, const uint64_t* d_offsets, uint64_t n, uint64_t chunk,

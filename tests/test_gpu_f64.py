@@ -145,3 +145,44 @@ def test_np_rejects_leading_one():
     comp.stream[0] |= 0x80
     with pytest.raises(api.DcbError):
         api.decompress_f64(comp)
+
+
+@pytest.mark.parametrize("ct", [5, 7])
+def test_long_single_chunk_statistics(ct):
+    """ONE chunk of >= 65,536 doubles takes the multi-block statistics (csrc/dcb_f64_stats_long.cuh): minimum with the reference's
+    first-occurrence rule, type / mask from max and mean, and the exact sequential mean when the bracket straddles a mask
+    boundary -- streams, min, mask and type bit for bit as the oracle's, on the shapes that exercise each rule."""
+    import torch
+    from data_compression_b200 import api
+    rng = np.random.default_rng(77)
+    n = 300001
+    sine = 5.0 + 4.5 * np.sin(2 * np.pi * (np.arange(1 << 18) % 65536) / 65536.0)      # mean - min = 4.5 exactly: a mask boundary
+    cases = {
+        "sine_boundary": sine,
+        "uniform": rng.random(n) * 10.0,
+        "walk": np.cumsum(rng.standard_normal(n)) * 0.02 + 100.0,
+        "min_is_last": np.concatenate([rng.random(n - 1) + 1.0, [0.5]]),
+        "min_is_first": np.concatenate([[0.25], rng.random(n - 1) + 1.0]),
+        "two_equal_minima": np.where(np.arange(n) % 100000 == 7, 0.125, rng.random(n) + 1.0),
+        "zeros_pos_then_neg": np.where(np.arange(n) == 70000, 0.0, np.where(np.arange(n) == 200000, -0.0, rng.random(n) + 1.0)),
+        "zeros_neg_then_pos": np.where(np.arange(n) == 70000, -0.0, np.where(np.arange(n) == 200000, 0.0, rng.random(n) + 1.0)),
+        "nan_inside": np.where(np.arange(n) == 123456, np.nan, rng.random(n) * 3.0),
+        "big": rng.random(n) * 1e200,
+        "constant": np.full(n, 0.123456789),
+    }
+    for name, x in cases.items():
+        for sub in (True, False):
+            try:
+                _check(x, ct, 1e-3, 0, subtract_min=sub, decode=(name != "nan_inside"))
+            except AssertionError as e:
+                raise AssertionError("%s subtract_min=%s: %s" % (name, sub, e))
+    # the exact mean itself (DCB_F_EXACT_MEDIUM), against the reference's sequential sum restated in numpy
+    dev = torch.device("cuda:0")
+    for name in ("sine_boundary", "uniform", "walk"):
+        x = cases[name]
+        comp = api.compress_f64(torch.from_numpy(x).to(dev), ct=7, abs_error_bound=1e-3, chunk_elems=0, exact_medium=True)
+        y = x - x.min()
+        total = 0.0
+        for v in y.tolist():
+            total += v
+        assert comp.chunk_medium[0].item() == total / y.size, name
