@@ -184,7 +184,16 @@ __device__ __forceinline__ void decode_round(LaneReader& br, const CodecConst& k
         c3 = c2; c2 = c1; c1 = x;
         t2 = t1; t1 = __fmul_rn(3.0f, x);
       }
-      if (!(neg >> 31)) {                  // no negative value -> none is the -1.0f marker: commit
+      // no negative value -> none is the -1.0f marker.  A negative one (closed-loop predictions drift below zero around a
+      // chunk's minimum, more often the smaller the bound) is only a reason to look: eight exact compares, then commit too
+      bool ok = !(neg >> 31);
+      if (!ok) {
+        bool mk = false;
+        #pragma unroll
+        for (int e = 0; e < DEC_RND; e++) mk = mk || (v[e] == -1.0f);
+        ok = !mk;
+      }
+      if (ok) {
         b1 = c1; b2 = c2; b3 = c3;
         br.consume(3 * DEC_RND);
         done = true;

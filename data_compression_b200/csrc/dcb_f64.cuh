@@ -614,7 +614,14 @@ __global__ void __launch_bounds__(128) dcb_f64_decode_kernel(F64DecArgs a) {
           neg |= (uint32_t)((uint64_t)__double_as_longlong(x) >> 32);
           c3 = c2; c2 = c1; c1 = x; t2 = t1; t1 = __dmul_rn(3.0, x);
         }
-        if (!(neg >> 31)) {
+        bool ok = !(neg >> 31);                                      // a negative value is only a reason to look for the marker
+        if (!ok) {
+          bool mk = false;
+          #pragma unroll
+          for (int e = 0; e < 8; e++) mk = mk || (x8[e] == -1.0);
+          ok = !mk;
+        }
+        if (ok) {
           b1 = c1; b2 = c2; b3 = c3;
           o += 24u;
           if (o >> 5) {                                              // at most one word
