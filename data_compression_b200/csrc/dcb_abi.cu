@@ -22,6 +22,7 @@
 #include "dcb_f64.cuh"
 #include "dcb_decode_single_f64.cuh"
 #include "dcb_f64_stats_long.cuh"
+#include "dcb_f64_decode_ring.cuh"
 #include "dcb_hamming.cuh"
 #include "dcb_bytewise.cuh"
 static int ensure_crc_tables(cudaStream_t st);
@@ -738,6 +739,21 @@ extern "C" int dcb_decompress_f64(int ct, const uint8_t* d_stream, const uint64_
     cudaError_t ef = cudaFreeAsync(ws, st);
     CK(e);
     CK(ef);
+    return DCB_OK;
+  }
+  // chunked streams: the ring decoder (dcb_f64_decode_ring.cuh; cp.async needs a 16-byte aligned stream).  DCB_F64_DECODER=window
+  // keeps the register-window kernel.
+  static const bool window_only = [] { const char* v = getenv("DCB_F64_DECODER"); return v && !strcmp(v, "window"); }();
+  if (!window_only && ((uintptr_t)d_stream & 15) == 0) {
+    const unsigned per_block = (F64R_NT / 32) * F64R_LANES;
+    const unsigned rgrid = (unsigned)((a.num_chunks + per_block - 1) / per_block);
+    switch (bct) {
+      case CT_BITWISE: dcb_f64_decode_ring_kernel<CT_BITWISE><<<rgrid, F64R_NT, 0, st>>>(a); break;
+      case CT_NP: dcb_f64_decode_ring_kernel<CT_NP><<<rgrid, F64R_NT, 0, st>>>(a); break;
+      case CT_MASK: dcb_f64_decode_ring_kernel<CT_MASK><<<rgrid, F64R_NT, 0, st>>>(a); break;
+      default: dcb_f64_decode_ring_kernel<CT_OP><<<rgrid, F64R_NT, 0, st>>>(a); break;
+    }
+    CK(cudaGetLastError());
     return DCB_OK;
   }
   const unsigned grid = (unsigned)((a.num_chunks + 4 * F64_DEC_LANES - 1) / (4 * F64_DEC_LANES));   // 4 warps per block
