@@ -166,6 +166,10 @@ int dcb_compress_f64(int ct, const double* d_in, uint64_t n, uint64_t chunk_elem
 int dcb_chunk_stats_f64(const double* d_in, uint64_t n, uint64_t chunk_elems, int subtract_min, int want_medium,
                         double* d_chunk_min, uint32_t* d_chunk_mask20, int32_t* d_chunk_type, double* d_chunk_medium,
                         void* cuda_stream);
+/* d_stream: 4-byte aligned at least.  When it is 16-byte aligned the decoder stages it in 16-byte blocks, and, as for float32, it
+ * must then be readable up to the next multiple of 16 bytes past d_chunk_offsets[K] (dcb_max_stream_bytes_f64 leaves that room).
+ * One chunk of more than 4096 elements (chunk_elems = 0 on a long array: the reference's own call shape) is decoded in parallel
+ * inside the chunk; its scratch comes from the library's stream-ordered memory pool. */
 int dcb_decompress_f64(int ct, const uint8_t* d_stream, const uint64_t* d_chunk_offsets, uint64_t n,
                        uint64_t chunk_elems, double abs_error_bound, uint32_t flags, int fixed_type,
                        uint32_t fixed_mask20, const double* d_chunk_min, const uint32_t* d_chunk_mask20,
