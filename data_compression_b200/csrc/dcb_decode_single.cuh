@@ -255,6 +255,23 @@ __device__ __forceinline__ float ds_step_exact(uint32_t op, float known, float& 
   return v;
 }
 
+// the 32 predicted values of a group once more, with exact compares against the -1.0f marker
+__device__ __noinline__ bool ds_group_has_marker(float c3, float c2, float c1, uint32_t mb, uint32_t mc) {
+  bool mk = false;
+  float u1 = __fmul_rn(3.0f, c1), u2 = __fmul_rn(3.0f, c2);
+  #pragma unroll 8
+  for (int e = 0; e < 32; e++) {
+    const float w = __fadd_rn(c1, c1);
+    const float d = __fsub_rn(u1, u2);
+    float x = c1;
+    if (mb & (1u << e)) x = __fsub_rn(w, c2);
+    if (mc & (1u << e)) x = __fadd_rn(d, c3);
+    mk = mk || (x == -1.0f);
+    c3 = c2; c2 = c1; c1 = x; u2 = u1; u1 = __fmul_rn(3.0f, x);
+  }
+  return mk;
+}
+
 // A thread walks every run that STARTS inside its DSR_G elements, each to the next run start (wherever that lies).  Known
 // elements are never written, so a neighbouring walker that reads the three values before its own start sees them unchanged.
 // Long runs (a smooth field is ONE run) are bound by the dependent float chain, so the walk keeps everything else off it:
@@ -309,7 +326,10 @@ __global__ void __launch_bounds__(128) dcb_resolve_kernel(const ResolveArgs a) {
             if ((e & 3) == 3) *reinterpret_cast<float4*>(out + j + e - 3) = make_float4(v[0], v[1], v[2], v[3]);
           }
           int r = 0;
-          if (((neg[0] | neg[1]) | (neg[2] | neg[3])) >> 31) {      // a negative value: maybe the marker -> exact state machine
+          // a negative value: look whether one IS the marker (closed-loop predictions drift below zero around a minimum, the
+          // marker itself is rare); out of line, so that the group's own code stays as it was
+          const bool mk = (((neg[0] | neg[1]) | (neg[2] | neg[3])) >> 31) && ds_group_has_marker(s3, s2, s1, mb, mc);
+          if (mk) {                                                 // the marker -> exact state machine
             b3 = s3; b2 = s2; b1 = s1;
             #pragma unroll 1
             for (int e = 0; e < 32; e++) {

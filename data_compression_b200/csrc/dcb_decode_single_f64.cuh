@@ -246,6 +246,23 @@ __device__ __forceinline__ double ds64_step_exact(uint32_t op, double known, dou
   return v;
 }
 
+// the 32 predicted values of a group once more, with exact compares against the -1.0 marker
+__device__ __noinline__ bool ds64_group_has_marker(double c3, double c2, double c1, uint32_t mb, uint32_t mc) {
+  bool mk = false;
+  double u1 = __dmul_rn(3.0, c1), u2 = __dmul_rn(3.0, c2);
+  #pragma unroll 8
+  for (int e = 0; e < 32; e++) {
+    const double w = __dadd_rn(c1, c1);
+    const double d = __dsub_rn(u1, u2);
+    double x = c1;
+    if (mb & (1u << e)) x = __dsub_rn(w, c2);
+    if (mc & (1u << e)) x = __dadd_rn(d, c3);
+    mk = mk || (x == -1.0);
+    c3 = c2; c2 = c1; c1 = x; u2 = u1; u1 = __dmul_rn(3.0, x);
+  }
+  return mk;
+}
+
 // As dcb_resolve_kernel: a thread walks every run that STARTS inside its 32 elements, each to the next run start.  Known
 // elements are never written, so a neighbouring walker that reads the three values before its own start sees them unchanged.
 __global__ void __launch_bounds__(128) dcb_resolve64_kernel(const Resolve64Args a) {
@@ -288,7 +305,9 @@ __global__ void __launch_bounds__(128) dcb_resolve64_kernel(const Resolve64Args 
             if (e & 1) *reinterpret_cast<double2*>(out + j + e - 1) = make_double2(v[0], v[1]);
           }
           int r = 0;
-          if (neg >> 31) {                                          // a negative value: maybe the marker -> exact state machine
+          // a negative value: look whether one IS the marker (out of line: the group's own code stays as it was)
+          const bool mk = (neg >> 31) && ds64_group_has_marker(s3, s2, s1, mb, mc);
+          if (mk) {                                                 // the marker -> exact state machine
             b3 = s3; b2 = s2; b1 = s1;
             #pragma unroll 1
             for (int e = 0; e < 32; e++) {
