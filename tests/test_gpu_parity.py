@@ -434,3 +434,39 @@ def test_stream_offsets_beyond_4_gib(dev):
     assert worst <= 1e-6 + 2 * 9.5367431640625e-07, worst
     del out, comp, x
     torch.cuda.empty_cache()
+
+
+def test_host_calls_with_large_pageable_buffers(dev):
+    """dcb_compress_host / dcb_decompress_host on plain numpy (malloc'd, pageable) arrays of more than 8 MB: bulk copies take the
+    staged path (four helpers, pinned staging, csrc/dcb_abi.cu copy_staged) -- sizes that are not a multiple of the 4 MB slice,
+    results identical to the device-resident calls; twice in a row (staging reused), and from two threads at once."""
+    import threading
+    n = 5 * (1 << 20) + 12345                                 # 20 MB + a ragged tail
+    x = np.concatenate([make_field("smooth", n // 2), make_field("noisy", n - n // 2)]).astype(np.float32)
+    comp = api.compress(torch.from_numpy(x).to(dev), ct=5, abs_error_bound=0.01, chunk_elems=4096, crc=True)
+    total = comp.total_bytes()
+    want_stream = comp.stream[:total].cpu().numpy()
+    want_out = api.decompress(comp).cpu().numpy()
+    for rep in range(2):
+        enc = api.compress_host(x, ct=5, abs_error_bound=0.01, chunk_elems=4096, crc=True)
+        assert enc["total_bytes"] == total
+        assert np.array_equal(enc["stream"][:total], want_stream)
+        assert np.array_equal(enc["chunk_crc"], comp.chunk_crc[:comp.num_chunks].cpu().numpy().view(np.uint32))
+        out = api.decompress_host(enc)
+        assert np.array_equal(out.view(np.uint32), want_out.view(np.uint32))
+    errs = []
+
+    def worker():
+        try:
+            e = api.compress_host(x, ct=5, abs_error_bound=0.01, chunk_elems=4096)
+            o = api.decompress_host(e)
+            if not np.array_equal(o.view(np.uint32), want_out.view(np.uint32)) or e["total_bytes"] != total:
+                errs.append("mismatch")
+        except Exception as ex:                               # noqa: BLE001
+            errs.append(repr(ex))
+    ts = [threading.Thread(target=worker) for _ in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errs, errs
