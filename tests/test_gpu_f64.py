@@ -186,3 +186,35 @@ def test_long_single_chunk_statistics(ct):
         for v in y.tolist():
             total += v
         assert comp.chunk_medium[0].item() == total / y.size, name
+
+
+@pytest.mark.parametrize("ct", [5, 6, 7, 11])
+def test_stream_that_is_only_4_byte_aligned(ct):
+    """dcb_decompress_f64 asks for a 4-byte aligned stream; the ring decoder needs 16 (cp.async), so a stream at 16k + 4 takes the
+    register-window kernel (csrc/dcb_f64.cuh dcb_f64_decode_kernel).  Same doubles bit for bit."""
+    import ctypes as C
+    import torch
+    from data_compression_b200 import api
+    dev = torch.device("cuda:0")
+    rng = np.random.default_rng(60 + ct)
+    n = 9 * 4096 + 321
+    x = np.concatenate([np.cumsum(rng.standard_normal(n // 2)) * 0.02 + 20.0, rng.random(n - n // 2) * 10.0])
+    comp = api.compress_f64(torch.from_numpy(x).to(dev), ct=ct, abs_error_bound=1e-3, chunk_elems=4096)
+    want = api.decompress_f64(comp)
+    total = comp.total_bytes()
+    buf = torch.zeros(total + 64, dtype=torch.uint8, device=dev)
+    buf[4:4 + total] = comp.stream[:total]
+    assert (buf.data_ptr() + 4) % 16 == 4
+    out = torch.empty(n, dtype=torch.float64, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    per_chunk = ct == 7
+    rc = api.lib().dcb_decompress_f64(ct, C.c_void_p(buf.data_ptr() + 4), C.c_void_p(comp.chunk_offsets.data_ptr()), n, 4096, 1e-3,
+                                      api.F_SUBTRACT_MIN, 0, 0, C.c_void_p(comp.chunk_min.data_ptr()),
+                                      C.c_void_p(comp.chunk_mask20.data_ptr()) if per_chunk else None,
+                                      C.c_void_p(comp.chunk_type.data_ptr()) if per_chunk else None,
+                                      C.c_void_p(out.data_ptr()), C.c_void_p(status.data_ptr()),
+                                      C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert status.item() == 0
+    assert torch.equal(out.view(torch.int64), want.view(torch.int64))
