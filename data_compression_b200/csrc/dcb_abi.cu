@@ -432,6 +432,7 @@ extern "C" int dcb_decompress(int ct, const uint8_t* d_stream, const uint64_t* d
   if (n == 0) return DCB_OK;
   const bool single = single_chunk(n, chunk);
   if (!single && (chunk % DCB_TILE) != 0) return DCB_EINVAL;
+  if (!single && chunk > (1ull << 26)) return DCB_EINVAL;            // a lane's bit position is 32 bits wide: <= 2^31 bits per chunk
   if (!d_stream || !d_offsets || !d_out || ((uintptr_t)d_stream & 15)) return DCB_EINVAL;
   if (n >= (1ull << 32) && single) return DCB_EINVAL;
   const bool per_chunk_mask = (bct == CT_MASK) && !(flags & DCB_F_FIXED_MASK);
@@ -744,7 +745,7 @@ extern "C" int dcb_decompress_f64(int ct, const uint8_t* d_stream, const uint64_
   // chunked streams: the ring decoder (dcb_f64_decode_ring.cuh; cp.async needs a 16-byte aligned stream).  DCB_F64_DECODER=window
   // keeps the register-window kernel.
   static const bool window_only = [] { const char* v = getenv("DCB_F64_DECODER"); return v && !strcmp(v, "window"); }();
-  if (!window_only && ((uintptr_t)d_stream & 15) == 0) {
+  if (!window_only && ((uintptr_t)d_stream & 15) == 0 && a.chunk <= (1ull << 25)) {   // (the ring reader's bit position is 32 bits wide)
     const unsigned per_block = (F64R_NT / 32) * F64R_LANES;
     const unsigned rgrid = (unsigned)((a.num_chunks + per_block - 1) / per_block);
     switch (bct) {

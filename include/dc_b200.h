@@ -53,7 +53,9 @@ int      dcb_device_count(void);
 
 /* to_absErrorBound_binary (dataCompression.c:5512): smallest n in [0,99] with eb >= 2^-n, else -1 */
 int      dcb_n_eb(double abs_error_bound);
-/* chunk_elems must be 0 (one chunk = whole array, the legacy call) or a multiple of DCB_TILE_ELEMS */
+/* chunk_elems must be 0 (one chunk = whole array, the legacy call) or a multiple of DCB_TILE_ELEMS; dcb_decompress takes chunked
+ * streams with chunk_elems <= 2^26 (a decoding lane's bit position is 32 bits wide); one chunk = whole array has no such limit
+ * below 2^32 elements (it is decoded in parallel inside the chunk). */
 uint64_t dcb_num_chunks(uint64_t n, uint64_t chunk_elems);
 /* worst case of the stream: every code is <= 32 bits */
 uint64_t dcb_max_stream_bytes(uint64_t n, uint64_t chunk_elems);

@@ -470,3 +470,14 @@ def test_host_calls_with_large_pageable_buffers(dev):
     for t in ts:
         t.join()
     assert not errs, errs
+
+
+def test_chunked_decode_rejects_chunks_beyond_the_lane_readers_range(dev):
+    """A decoding lane keeps its bit position in 32 bits: dcb_decompress refuses chunked streams with more than 2^26 elements per
+    chunk (DCB_EINVAL) instead of wrapping; argument checks come before any memory is touched."""
+    import ctypes as C
+    d = torch.zeros(64, dtype=torch.uint8, device=dev)
+    p = C.c_void_p(d.data_ptr())
+    rc = api.lib().dcb_decompress(5, p, p, (1 << 28) + 1, 1 << 27, 0.01, 0, 0, 0, None, None, None, p, None,
+                                  C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+    assert rc == -1, rc
