@@ -257,8 +257,11 @@ __device__ __forceinline__ void decode_round(LaneReader& br, const CodecConst& k
 #define DEC_OPITCH 36               // floats per lane row of the output staging (144 B: conflict-free 128-bit accesses)
 #define DEC_SMEM_BYTES (DEC_NT * (DEC_PITCH + DEC_OPITCH) * 4)
 
+#ifndef DEC_MIN_BLOCKS
+#define DEC_MIN_BLOCKS (DEC_RING_BLOCKS > 8 ? 4 : 6)
+#endif
 template <int CT>
-__global__ void __launch_bounds__(DEC_NT, (DEC_RING_BLOCKS > 8 ? 4 : 6)) dcb_decode_kernel(const DecArgs a) {
+__global__ void __launch_bounds__(DEC_NT, DEC_MIN_BLOCKS) dcb_decode_kernel(const DecArgs a) {
   extern __shared__ __align__(16) unsigned char dec_smem[];          // DEC_SMEM_BYTES: per-lane stream rings, then the output staging
   uint32_t* const rings = reinterpret_cast<uint32_t*>(dec_smem);
   float* const ostage = reinterpret_cast<float*>(dec_smem + DEC_NT * DEC_PITCH * 4);
