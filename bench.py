@@ -248,6 +248,8 @@ def sweep_plan(kind, log2n):
             plan.append((ct, f, n, 0.01, 4096))
     for ct in (5, 7):
         plan.append((ct, "smooth", 1 << 30, 0.01, 4096))
+    for ct in (8, 9):
+        plan.append((ct, "noisy", 1 << 30, 0.01, 4096))          # BASELINE.json configs[4] at its own size, on one GPU
     for ct in (5, 7, 6, 11):
         plan.append((ct, "smooth", 131072, 0.01, 0))            # pingpong shape, one chunk (legacy call)
     plan.append((5, "noisy", 131072, 0.01, 0))
